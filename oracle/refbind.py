@@ -1,0 +1,136 @@
+"""ctypes bindings of oracle/_ref/libsgm_ref.so — the reference's own CPU sources
+(/root/reference/src/{Solver,SGM,BM,cost}.cpp) compiled unmodified by oracle/Makefile.
+
+TEST INFRASTRUCTURE: the checker, never the thing measured as the product.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_ref", "libsgm_ref.so")
+
+_u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+_lib = None
+
+
+def available() -> bool:
+    return os.path.exists(LIB_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not available():
+            raise RuntimeError(f"{LIB_PATH} missing: run `make -C oracle ref` where /root/reference exists")
+        L = C.CDLL(LIB_PATH)
+        L.ref_process.restype = C.c_double
+        L.ref_process.argtypes = [C.c_int] * 5 + [C.c_void_p] * 9
+        L.ref_time_process.restype = C.c_int
+        L.ref_time_process.argtypes = [C.c_int] * 5 + [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.ref_stages.restype = C.c_int
+        L.ref_stages.argtypes = [C.c_int] * 5 + [C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 5
+        L.ref_cost_volume.restype = C.c_int
+        L.ref_cost_volume.argtypes = [C.c_int] * 7 + [C.c_void_p] * 3
+        L.ref_hamming_cost.restype = C.c_int
+        L.ref_hamming_cost.argtypes = [C.c_uint64, C.c_uint64]
+        L.ref_gaussian_blur.restype = C.c_int
+        L.ref_gaussian_blur.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_double]
+        L.ref_set_threads.argtypes = [C.c_int]
+        L.ref_set_quiet.argtypes = [C.c_int]
+        L.ref_max_threads.restype = C.c_int
+        _lib = L
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _u8(a):
+    return None if a is None else np.ascontiguousarray(a, dtype=np.uint8)
+
+
+def set_threads(n: int):
+    lib().ref_set_threads(int(n))
+
+
+def max_threads() -> int:
+    return lib().ref_max_threads()
+
+
+ALGO = {"sgm": 0, "bm": 1}
+
+
+def process(algo, left, right, scale, d, sky_l=None, sky_r=None, want_cost=False):
+    """Runs SGM::process / BM::process of the reference.  Returns a dict of numpy arrays + 'ms'."""
+    left, right = _u8(left), _u8(right)
+    h, w = left.shape
+    ih, iw = h // scale, w // scale
+    sky_l, sky_r = _u8(sky_l), _u8(sky_r)
+    out = dict(
+        disp=np.zeros((ih, iw), np.uint8),
+        disp_beta=np.zeros((ih, iw), np.uint8),
+        fdisp=np.zeros((ih, iw), np.float32),
+        fdisp_beta=np.zeros((ih, iw), np.float32),
+    )
+    cost = np.zeros((ih, iw, d), np.float32) if want_cost else None
+    ms = lib().ref_process(ALGO[algo], h, w, scale, d, _p(left), _p(right), _p(sky_l), _p(sky_r), _p(out["disp"]),
+                           _p(out["disp_beta"]), _p(out["fdisp"]), _p(out["fdisp_beta"]), _p(cost))
+    if ms < 0:
+        raise RuntimeError("ref_process failed")
+    out["ms"] = ms
+    if want_cost:
+        out["cost_last"] = cost
+    return out
+
+
+def time_process(algo, left, right, scale, d, iters):
+    left, right = _u8(left), _u8(right)
+    h, w = left.shape
+    ms = np.zeros(iters, np.float64)
+    rc = lib().ref_time_process(ALGO[algo], h, w, scale, d, _p(left), _p(right), iters, _p(ms))
+    if rc != 0:
+        raise RuntimeError("ref_time_process failed")
+    return ms
+
+
+def stages(algo, left, right, scale, d, beta=False, sky=None):
+    """Intermediate taps: census tables, raw / h-filtered / hv-filtered cost volume of one view."""
+    left, right = _u8(left), _u8(right)
+    h, w = left.shape
+    ih, iw = h // scale, w // scale
+    sky = _u8(sky)
+    out = dict(
+        ct_l=np.zeros((ih, iw), np.uint64),
+        ct_r=np.zeros((ih, iw), np.uint64),
+        cost_raw=np.zeros((ih, iw, d), np.float32),
+        cost_h=np.zeros((ih, iw, d), np.float32),
+        cost_hv=np.zeros((ih, iw, d), np.float32),
+    )
+    rc = lib().ref_stages(ALGO[algo], h, w, scale, d, _p(left), _p(right), _p(sky), int(beta), _p(out["ct_l"]),
+                          _p(out["ct_r"]), _p(out["cost_raw"]), _p(out["cost_h"]), _p(out["cost_hv"]))
+    if rc != 0:
+        raise RuntimeError("ref_stages failed")
+    return out
+
+
+def cost_volume(kind, left, right, d, win_h, win_w, scale=1):
+    left, right = _u8(left), _u8(right)
+    h, w = left.shape
+    out = np.zeros((h, w, d), np.float32)
+    rc = lib().ref_cost_volume({"sad": 0, "ssd": 1, "ct": 2}[kind], h, w, d, win_h, win_w, scale, _p(left), _p(right),
+                               _p(out))
+    if rc != 0:
+        raise RuntimeError("ref_cost_volume failed")
+    return out
+
+
+def gaussian_blur(img, sx=2.0, sy=1.0):
+    img = _u8(img)
+    out = np.zeros_like(img)
+    lib().ref_gaussian_blur(img.shape[0], img.shape[1], _p(img), _p(out), float(sx), float(sy))
+    return out
