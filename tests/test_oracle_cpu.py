@@ -1,0 +1,119 @@
+"""CPU tests of the oracle (-m "not gpu"): the restatement (oracle/sgm_oracle.c) is pinned against
+(1) the committed golden vectors produced by the reference itself (tests/golden/, made by
+make_golden.py from oracle/_ref = the unmodified /root/reference sources) and (2), where the compiled
+reference is present, live runs of it on fresh random inputs; the blur stand-in is pinned against cv2."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import refbind, restate
+from stereo_matching_b200 import synth
+from tests.common import bits_equal, case_inputs, n_diff
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+H = restate.fnv1a64
+
+
+def test_generator_matches_std_mt19937():
+    # first outputs of std::mt19937(1234); the KAT hashes of SURVEY.md 8(c) depend on it
+    L, R, gt = synth.random_dot_pair(4, 8, seed=1234)
+    assert R.ravel()[:3].tolist() == [822569775 & 255, 2137449171 & 255, 2671936806 & 255]
+    assert synth.fnv1a64(R) == H(R)
+
+
+def test_blur_restatement_matches_cv2():
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.RandomState(0)
+    for shp in [(16, 16), (375, 1242), (37, 53), (1, 9), (9, 1), (2, 2)]:
+        img = rng.randint(0, 256, size=shp).astype(np.uint8)
+        want = cv2.GaussianBlur(img, (3, 3), 2, sigmaY=1)
+        got = restate.process(img, img, 1, 32, "sgm", taps=("blur",))["blur"][0] if min(shp) >= 8 else None
+        if got is not None:
+            assert bits_equal(got, want), shp
+        if refbind.available():
+            assert bits_equal(refbind.gaussian_blur(img), want), shp
+
+
+def test_survey_known_answers(golden):
+    # SURVEY.md 8(c) quotes these for the reference on the mt19937(1234) pair
+    h = golden["kitti_sgm_d128_clean"]["hashes"]
+    assert (h["disp"], h["disp_beta"], h["f_final"]) == ("13c4a67b7e022475", "6d8bb4348527823e", "233489a1f55f2e3f")
+    h = golden["kitti_sgm_d64_clean"]["hashes"]
+    assert (h["disp"], h["disp_beta"], h["f_final"]) == ("89ff0b11223194b5", "6b8a0eb1f5555b26", "6c9b06a2424d5188")
+    assert golden["kitti_bm_d64_clean"]["hashes"]["disp"] == "06a66f0562967f35"
+
+
+FULL = ["kitti_sgm_d128_clean", "kitti_sgm_d128_noisy_sky", "kitti_sgm_d64_noisy", "kitti_sgm_d64_scale2",
+        "kitti_bm_d64_noisy", "odd_sgm_d32", "tall_sgm_d32"]
+
+
+@pytest.mark.parametrize("name", FULL)
+def test_restatement_against_golden(golden, name):
+    c = golden[name]
+    L, R, (sl, sr) = case_inputs(c)
+    want = c["hashes"]
+    assert (H(L), H(R)) == (want["left"], want["right"])
+    out = restate.process(L, R, c["scale"], c["d"], c["algo"], sl, sr, taps=restate.ALL_TAPS)
+    got = dict(census_l=H(out["census"][0]), census_r=H(out["census"][1]), cost_raw_l=H(out["cost_raw"][0]),
+               cost_h_l=H(out["cost_h"][0]), cost_hv_l=H(out["cost_hv"][0]), disp=H(out["disp"][0].astype(np.uint8)))
+    if c["algo"] == "sgm":
+        got.update(cost_raw_r=H(out["cost_raw"][1]), cost_hv_r=H(out["cost_hv"][1]), S_r=H(out["S"][1]),
+                   disp_beta=H(out["disp"][1].astype(np.uint8)), fsub_r=H(out["fsub"][1]), f_final=H(out["f_final"]))
+    for k, v in got.items():
+        assert v == want[k], f"{name}: stage {k} differs from the reference"
+
+
+def test_small_fixture_arrays():
+    z = np.load(os.path.join(GOLD, "small_sgm.npz"))
+    d = int(z["d"])
+    out = restate.process(z["left"], z["right"], 1, d, "sgm", taps=restate.ALL_TAPS)
+    assert bits_equal(out["census"][0], z["census_l"]) and bits_equal(out["census"][1], z["census_r"])
+    assert bits_equal(out["cost_hv"][0], z["cost_hv_l"]) and bits_equal(out["cost_hv"][1], z["cost_hv_r"])
+    assert bits_equal(out["S"][1], z["S_r"])
+    assert bits_equal(out["disp"][0].astype(np.uint8), z["disp"])
+    assert bits_equal(out["disp"][1].astype(np.uint8), z["disp_beta"])
+    assert bits_equal(out["fsub"][1], z["fsub_r"]) and bits_equal(out["f_final"], z["f_final"])
+    b = np.load(os.path.join(GOLD, "small_bm.npz"))
+    ob = restate.process(b["left"], b["right"], 1, d, "bm")
+    assert bits_equal(ob["disp"][0].astype(np.uint8), b["disp"])
+
+
+@pytest.mark.skipif(not refbind.available(), reason="compiled reference (oracle/_ref) not present")
+@pytest.mark.parametrize("h,w,d,scale,noise,sky", [(96, 160, 32, 1, 6, False), (120, 200, 64, 1, 40, True),
+                                                   (200, 320, 64, 2, 10, True), (64, 300, 128, 1, 25, False)])
+def test_restatement_against_live_reference(h, w, d, scale, noise, sky):
+    L, R, _ = synth.random_dot_pair(h, w, seed=h * 7 + d, bg=5, fg=min(17, d // 2), noise=noise)
+    sl, sr = synth.sky_masks(h // scale, w // scale) if sky else (None, None)
+    refbind.set_threads(1)
+    ref = refbind.process("sgm", L, R, scale, d, sl, sr, want_cost=True)
+    out = restate.process(L, R, scale, d, "sgm", sl, sr, taps=restate.ALL_TAPS)
+    for beta, m in ((False, sl), (True, sr)):
+        st = refbind.stages("sgm", L, R, scale, d, beta=beta, sky=m)
+        v = int(beta)
+        assert bits_equal(st["cost_raw"], out["cost_raw"][v]) and bits_equal(st["cost_h"], out["cost_h"][v])
+        assert bits_equal(st["cost_hv"], out["cost_hv"][v])
+    assert bits_equal(ref["cost_last"], out["S"][1])
+    assert n_diff(ref["disp"], out["disp"][0]) == 0 and n_diff(ref["disp_beta"], out["disp"][1]) == 0
+    assert bits_equal(ref["fdisp_beta"], out["fsub"][1]) and bits_equal(ref["fdisp"], out["f_final"])
+    # reference BM (census + box + WTA with |dd| > 2)
+    rb = refbind.process("bm", L, R, scale, d, sl, sr)
+    ob = restate.process(L, R, scale, d, "bm", sl, sr)
+    assert n_diff(rb["disp"], ob["disp"][0]) == 0
+
+
+@pytest.mark.skipif(not refbind.available(), reason="compiled reference (oracle/_ref) not present")
+def test_sad_volume_against_reference_function():
+    # oracle's SAD volume vs the reference's own SAD() (src/cost.cpp:4-30) evaluated per pixel
+    L, R, _ = synth.random_dot_pair(24, 40, seed=2, bg=3, fg=7, noise=12)
+    want = refbind.cost_volume("sad", L, R, 16, 9, 9)
+    got = restate.process(L, R, 1, 16, "bm_sad", taps=("cost_raw",))["cost_raw"][0]
+    assert bits_equal(want, got)
+
+
+def test_widened_restatement_runs_d256():
+    # D=256 cannot run through the reference (src/Solver.cpp:10 asserts); the restatement is the oracle there
+    L, R, _ = synth.random_dot_pair(48, 400, seed=4, bg=24, fg=200, noise=4)
+    out = restate.process(L, R, 1, 256, "sgm")
+    f = out["f_final"]
+    assert out["disp"][0].max() <= 257 and (f <= 255).sum() > 0
