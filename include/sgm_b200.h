@@ -1,0 +1,157 @@
+/* sgm_b200.h — C ABI of the B200-native stereo matching engine (libsgm_b200.so).
+ *
+ * This is the drop-in boundary for the reference's dense-stereo hot path.  The reference
+ * (hilbertw/stereo_matching) runs that path on the CPU inside its Solver / SGM / BM classes
+ * (inc/Solver.h:23-70, inc/SGM.h:10-27, inc/BM.h:6-18); here it runs as hand-written sm_100a
+ * CUDA kernels behind an opaque handle.  The C++ shells in stereo_matching_b200/host/ keep the
+ * reference class surface and forward to these entry points; INTEGRATION.md shows the binding.
+ *
+ * Conventions: plain pointers and sizes only; host pointers unless a name says `_device`;
+ * strides are in BYTES; every call returns 0 (SGM_OK) or an sgm_status error code and never aborts;
+ * sgm_last_error() gives the message.  One handle processes one frame at a time and is not
+ * thread-safe; distinct handles are independent (one per GPU / per in-flight frame).
+ * There is NO CPU fallback: without a CUDA device sgm_create() fails with SGM_ERR_CUDA.
+ */
+#ifndef SGM_B200_H_
+#define SGM_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SGM_B200_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define SGM_API __attribute__((visibility("default")))
+#else
+#define SGM_API
+#endif
+
+typedef struct sgm_engine sgm_engine; /* opaque */
+
+typedef enum sgm_status {
+    SGM_OK = 0,
+    SGM_ERR_INVALID = 1,     /* bad argument / shape (the reference would assert: src/Solver.cpp:6-10, src/SGM.cpp:34-38) */
+    SGM_ERR_UNSUPPORTED = 2, /* parameter combination the kernels are not built for */
+    SGM_ERR_CUDA = 3,        /* CUDA runtime error, or no device */
+    SGM_ERR_NOMEM = 4,
+    SGM_ERR_STATE = 5        /* result requested before any frame was processed */
+} sgm_status;
+
+typedef enum sgm_algo {
+    SGM_ALGO_SGM = 0,    /* SGM::process  (src/SGM.cpp:32-826): census + recursive box + 4/8-path SGM, both views, LR, post filter */
+    SGM_ALGO_BM = 1,     /* BM::process   (src/BM.cpp:9-97): census + recursive box + WTA(|dd|>2), left view, post filter */
+    SGM_ALGO_BM_SAD = 2  /* SAD block matching built from SAD() (src/cost.cpp:4-30): both views, WTA(|dd|>2), LR, post filter */
+} sgm_algo;
+
+/* Replaces the compile-time constants of inc/Solver.h:10-20, inc/SGM.h:7 and src/SGM.cpp:27-28
+ * and the ctor arguments Solver(h, w, s, d) (src/Solver.cpp:4-16).  sgm_default_params() fills
+ * the reference's values. */
+typedef struct sgm_params {
+    int32_t height, width;       /* full-resolution input size (ctor h, w) */
+    int32_t scale;               /* 1 or 2: nearest-neighbour decimation before matching */
+    int32_t max_disp;            /* D: 32, 64, 128 (reference) or 256 (widened, uint16 disparity) */
+    int32_t algo;                /* sgm_algo */
+    int32_t paths;               /* 4 or 8 aggregation paths (USE_8_PATH) */
+    int32_t P1, P2;              /* SGM penalties (10, 100) */
+    int32_t census_h, census_w;  /* WIN_H, WIN_W = 7, 9 (divided by scale at use, like the reference) */
+    int32_t box_w, box_h;        /* COST_WIN_W, COST_WIN_H = 5, 3 (divided by scale at use) */
+    float unique_ratio;          /* UNIQUE_RATIO = 0.7 */
+    float lr_thresh;             /* LR_CHECK_DIS = 1 */
+    int32_t median_h, median_w;  /* MEDIAN_FILTER_H/W = 5, 5 */
+    int32_t speckle_size;        /* SPECKLE_SIZE = 1000 (divided by scale at use) */
+    int32_t speckle_dis;         /* SPECKLE_DIS = 2 */
+    int32_t sad_h, sad_w;        /* SAD window (9, 9) for SGM_ALGO_BM_SAD (divided by scale at use) */
+    int32_t device;              /* CUDA device ordinal */
+    uint32_t flags;              /* SGM_FLAG_* */
+} sgm_params;
+
+#define SGM_FLAG_KEEP_VOLUMES 0x1u /* keep the summed path volume S of both views readable through sgm_get_tap (debug; costs 4 B per disp.px) */
+#define SGM_FLAG_STAGE_TIMING 0x2u /* record CUDA events around the pipeline stages on the engine's stream (sgm_get_stage_ms) */
+
+/* Buffers readable after a frame, for parity tests and debugging (the reference keeps the same data in
+ * Solver's protected members, inc/Solver.h:43-52).  view: 0 = left, 1 = right ("beta"). */
+typedef enum sgm_tap {
+    SGM_TAP_CENSUS = 0,    /* uint64 [ih*iw]       cost_table_l (view 0) / cost_table_r (view 1) */
+    SGM_TAP_COST = 1,      /* float  [ih*iw*D]     cost volume after both box filters (SAD volume for BM_SAD) */
+    SGM_TAP_PATHSUM = 2,   /* float  [ih*iw*D]     summed path volume S (needs SGM_FLAG_KEEP_VOLUMES) */
+    SGM_TAP_DISP = 3,      /* uint16 [ih*iw]       WTA + uniqueness disparity, invalid = D+1 (Solver::disp / disp_beta) */
+    SGM_TAP_SUBPIXEL = 4,  /* float  [ih*iw]       compute_subpixel output before the LR-check */
+    SGM_TAP_LR = 5,        /* float  [ih*iw]       left view after the LR-check (view must be 0) */
+    SGM_TAP_MEDIAN = 6,    /* float  [ih*iw]       left view after the hole-filling median (view must be 0) */
+    SGM_TAP_FINAL = 7,     /* float  [ih*iw]       left view after the speckle filter == Solver::get_disp() */
+    SGM_TAP_BLUR = 8       /* uint8  [ih*iw]       Gaussian-blurred input */
+} sgm_tap;
+
+typedef enum sgm_stage {
+    SGM_STAGE_UPLOAD = 0,     /* H2D of the inputs */
+    SGM_STAGE_COST = 1,       /* subsample, blur, census, Hamming/SAD volume, recursive box filters */
+    SGM_STAGE_AGGREGATE = 2,  /* all path kernels incl. the fused sum/WTA/uniqueness/sub-pixel epilogue */
+    SGM_STAGE_POST = 3,       /* LR-check, hole-filling median, speckle filter */
+    SGM_STAGE_DOWNLOAD = 4,   /* D2H of the result */
+    SGM_STAGE_COUNT = 5
+} sgm_stage;
+
+SGM_API void sgm_default_params(sgm_params* p, int height, int width, int scale, int max_disp, int algo);
+
+/* Solver::Solver / SGM::SGM / BM::BM (src/Solver.cpp:4-52, src/SGM.cpp:4-29): validates, allocates all
+ * device volumes, pinned staging and the stream. */
+SGM_API int sgm_create(sgm_engine** out, const sgm_params* params);
+/* Solver::~Solver / SGM::~SGM (src/Solver.cpp:710-719, src/SGM.cpp:837-858). */
+SGM_API void sgm_destroy(sgm_engine* e);
+/* Message of the last error on this handle; with e == NULL, of the last failed sgm_create on this thread. */
+SGM_API const char* sgm_last_error(const sgm_engine* e);
+
+/* Solver::process(img_l, img_r, sky_mask, sky_mask_beta) (src/SGM.cpp:829-834, src/BM.cpp:100-105): host
+ * images in (8-bit, `height` x `width`, row strides in bytes), blocking; the result is then available from
+ * the getters.  sky_l / sky_r may be NULL (Solver::process(img_l, img_r)); when given they are
+ * (height/scale) x (width/scale) masks with 255 = sky (src/Solver.cpp:146-179). */
+SGM_API int sgm_process(sgm_engine* e, const uint8_t* left, size_t left_stride, const uint8_t* right, size_t right_stride,
+                const uint8_t* sky_l, size_t sky_l_stride, const uint8_t* sky_r, size_t sky_r_stride);
+
+/* Asynchronous pair for the frame-stream runner: sgm_enqueue copies the inputs into the handle's pinned
+ * staging, queues H2D + all kernels + D2H on the handle's stream and returns; sgm_wait blocks until done. */
+SGM_API int sgm_enqueue(sgm_engine* e, const uint8_t* left, size_t left_stride, const uint8_t* right, size_t right_stride,
+                const uint8_t* sky_l, size_t sky_l_stride, const uint8_t* sky_r, size_t sky_r_stride);
+SGM_API int sgm_wait(sgm_engine* e);
+
+/* Same pipeline with inputs already resident in device memory (no H2D, no D2H): queues the kernels on the
+ * handle's stream and returns; follow with sgm_wait.  Pointers are device pointers on the handle's device. */
+SGM_API int sgm_enqueue_device(sgm_engine* e, const void* left_device, size_t left_stride, const void* right_device,
+                       size_t right_stride, const void* sky_l_device, size_t sky_l_stride, const void* sky_r_device,
+                       size_t sky_r_stride);
+
+/* Solver::get_disp() (inc/Solver.h:36): the final float disparity (invalid = D+1), (height/scale) x (width/scale). */
+SGM_API int sgm_get_disparity_f32(sgm_engine* e, float* dst, size_t dst_stride);
+/* Solver::disp / disp_beta narrowed to 8 bits like the reference's CV_8UC1 Mats (only for D <= 128). */
+SGM_API int sgm_get_disparity_u8(sgm_engine* e, int view, uint8_t* dst, size_t dst_stride);
+SGM_API int sgm_get_disparity_u16(sgm_engine* e, int view, uint16_t* dst, size_t dst_stride);
+/* Device pointer of the final float disparity (valid until the next frame), for device-side consumers. */
+SGM_API const float* sgm_disparity_device(sgm_engine* e);
+
+/* Debug / parity taps: copies tap `which` of `view` into dst (bytes must equal sgm_tap_bytes). */
+SGM_API size_t sgm_tap_bytes(const sgm_engine* e, int which);
+SGM_API int sgm_get_tap(sgm_engine* e, int which, int view, void* dst, size_t bytes);
+
+/* Introspection for bench.py: working size, kernel launches of the last frame, per-stage device times of the
+ * last frame (needs SGM_FLAG_STAGE_TIMING), the CUDA stream (cudaStream_t) the kernels are launched on. */
+SGM_API int sgm_get_size(const sgm_engine* e, int* out_h, int* out_w, int* out_d);
+SGM_API int sgm_get_launch_count(const sgm_engine* e);
+SGM_API int sgm_get_stage_ms(sgm_engine* e, float* ms, int count);
+SGM_API void* sgm_get_stream(sgm_engine* e);
+SGM_API size_t sgm_device_bytes(const sgm_engine* e);
+
+/* Dense forms of the free functions of inc/cost.h:7-14 (SAD / census), computed on the device:
+ * out is a host float volume [ih][iw][D], as Solver::build_dsi (src/Solver.cpp:96-117) would fill it. */
+SGM_API int sgm_cost_volume_sad(int device, const uint8_t* left, const uint8_t* right, int height, int width, int max_disp,
+                        int win_h, int win_w, int scale, float* out);
+
+SGM_API int sgm_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SGM_B200_H_ */

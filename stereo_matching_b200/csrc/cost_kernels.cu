@@ -1,0 +1,308 @@
+// cost_kernels.cu — cost-volume construction for sm_100a: decimation, Gaussian pre-blur, census
+// transform, Hamming volume fused with the reference's recursive horizontal cost filter, the recursive
+// vertical filter, and the SAD volume.
+//
+// Replaces Solver::build_cost_table / build_dsi_from_table(_beta) / cost_horizontal_filter /
+// cost_vertical_filter (src/Solver.cpp:120-368), CT_pts / hamming_cost / SAD (src/cost.cpp) of the reference.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace sgmb200 {
+
+namespace {
+
+// ---------------------------------------------------------------------------------------------
+// src/SGM.cpp:40-56 (rows i*scale) / src/BM.cpp:17-33 (rows i): nearest-neighbour decimation into a
+// dense [2][ih*iw] buffer; with scale == 1 this is just the pitched -> dense copy.
+__global__ void subsample_kernel(const uint8_t* __restrict__ src, size_t src_stride, int col_step, int row_step,
+                                 uint8_t* __restrict__ dst, int ih, int iw) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    if (j >= iw || i >= ih) return;
+    dst[(size_t)i * iw + j] = src[(size_t)(i * row_step) * src_stride + (size_t)j * col_step];
+}
+
+// ---------------------------------------------------------------------------------------------
+// src/Solver.cpp:124-125: cv::GaussianBlur(img, out, Size(3,3), 2, 1) on CV_8U.  OpenCV runs this in
+// fixed point: kx = [82,92,82]/256, ky = [70,116,70]/256, (v + 2^15) >> 16, BORDER_REFLECT_101.
+__device__ __forceinline__ int reflect101(int p, int n) {
+    if (n == 1) return 0;
+    if (p < 0) return -p;
+    if (p >= n) return 2 * n - 2 - p;
+    return p;
+}
+__global__ void blur3_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, int h, int w) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    if (j >= w) return;
+    const size_t img = (size_t)blockIdx.z * h * w;
+    const uint8_t* s = src + img;
+    const int jm = reflect101(j - 1, w), jp = reflect101(j + 1, w);
+    const int rows[3] = {reflect101(i - 1, h), i, reflect101(i + 1, h)};
+    int hsum[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+        const uint8_t* row = s + (size_t)rows[r] * w;
+        hsum[r] = 82 * (int)__ldg(row + jm) + 92 * (int)__ldg(row + j) + 82 * (int)__ldg(row + jp);
+    }
+    dst[img + (size_t)i * w + j] = (uint8_t)((70 * hsum[0] + 116 * hsum[1] + 70 * hsum[2] + 32768) >> 16);
+}
+
+// ---------------------------------------------------------------------------------------------
+// src/cost.cpp:99-129 (CT_pts): (2*rh+1) x (2*rw+1) census, replicate-clamped coordinates, centre skipped,
+// bit = neighbour > centre appended as (v << 1) | bit in row-major order.  The image tile plus halo is
+// staged in shared memory so the 62 compares per pixel read on-chip data.
+constexpr int CT_TX = 32, CT_TY = 8, CT_MAX_RH = 3, CT_MAX_RW = 4;
+__global__ void census_kernel(const uint8_t* __restrict__ img, uint64_t* __restrict__ table, int h, int w, int rh, int rw) {
+    __shared__ uint8_t tile[CT_TY + 2 * CT_MAX_RH][CT_TX + 2 * CT_MAX_RW];
+    const size_t base = (size_t)blockIdx.z * h * w;
+    const uint8_t* s = img + base;
+    const int x0 = blockIdx.x * CT_TX, y0 = blockIdx.y * CT_TY;
+    const int tw = CT_TX + 2 * rw, th = CT_TY + 2 * rh;
+    for (int t = threadIdx.y * CT_TX + threadIdx.x; t < tw * th; t += CT_TX * CT_TY) {
+        const int ty = t / tw, tx = t % tw;
+        const int y = min(max(y0 + ty - rh, 0), h - 1);
+        const int x = min(max(x0 + tx - rw, 0), w - 1);
+        tile[ty][tx] = __ldg(s + (size_t)y * w + x);
+    }
+    __syncthreads();
+    const int x = x0 + threadIdx.x, y = y0 + threadIdx.y;
+    if (x >= w || y >= h) return;
+    const uint8_t ctr = tile[threadIdx.y + rh][threadIdx.x + rw];
+    uint64_t v = 0;
+    for (int a = 0; a <= 2 * rh; ++a)
+        for (int b = 0; b <= 2 * rw; ++b) {
+            if (a == rh && b == rw) continue;
+            v = (v << 1) | (uint64_t)(tile[threadIdx.y + a][threadIdx.x + b] > ctr);
+        }
+    table[base + (size_t)y * w + x] = v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The reference's cost filters run IN PLACE (src/Solver.cpp:319,325 and :357,363): once the running sum
+// starts subtracting "the value WIN columns back", that column has already been overwritten with its
+// filtered value, so the filter is a float recurrence along the line, not a box mean.
+// RecBox reproduces it as a stream: values are fed in line order; it tracks the final value of every
+// position (raw for the first FIRST positions, filtered afterwards) in a FIRST+1 deep shift register, whose
+// oldest entry is exactly what the reference subtracts.  Operation order per step: add, subtract, divide.
+template <int WIN>
+struct RecBox {
+    static constexpr int HALF = WIN / 2;
+    static constexpr int FIRST = WIN - HALF - 1;  // first filtered position
+    static constexpr int R = FIRST + 1;
+    float ring[R];
+    float sum;
+    __device__ __forceinline__ void reset() {
+        sum = 0.f;
+#pragma unroll
+        for (int r = 0; r < R; ++r) ring[r] = 0.f;
+    }
+    __device__ __forceinline__ void push(float v) {
+#pragma unroll
+        for (int r = 0; r + 1 < R; ++r) ring[r] = ring[r + 1];
+        ring[R - 1] = v;
+    }
+    // Feeds the raw value of position p (0-based, in order).  Returns true when a filtered value for position
+    // `out_pos` is produced.  `len` is the line length.
+    __device__ __forceinline__ bool feed(int p, float c, int len, int& out_pos, float& out_val) {
+        sum = __fadd_rn(sum, c);
+        if (p >= WIN) sum = __fsub_rn(sum, ring[0]);
+        if (p < FIRST) push(c);  // leading positions stay raw: their final value is the raw one
+        if (p >= WIN - 1) {
+            const int pos = FIRST + (p - (WIN - 1));
+            const int last = FIRST + (len - 2 * HALF) - 1;
+            if (pos <= last) {
+                out_val = __fdiv_rn(sum, (float)WIN);
+                out_pos = pos;
+                push(out_val);
+                return true;
+            }
+        }
+        return false;
+    }
+    __device__ static __forceinline__ int last_filtered(int len) { return FIRST + (len - 2 * HALF) - 1; }
+};
+
+// src/Solver.cpp:143-248 (Hamming volume of one view, sky override) fused with :296-330 (horizontal filter).
+// One thread per (row, d) marches along j; a warp covers 32 consecutive d of one row, so the left census word
+// is a broadcast load, the right one a contiguous (reversed) 256-byte load, and every store is a coalesced
+// 128-byte line of the [i][j][d] volume.
+template <int WIN>
+__global__ void __launch_bounds__(128) hamming_hfilter_kernel(const uint64_t* __restrict__ ct_l,
+                                                              const uint64_t* __restrict__ ct_r,
+                                                              const uint8_t* __restrict__ sky_l,
+                                                              const uint8_t* __restrict__ sky_r,
+                                                              float* __restrict__ cost, int h, int w, int d, int scale) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= h * d) return;
+    const int view = blockIdx.y;
+    const int i = g / d, k = g % d;
+    const int shift = k / scale;
+    const uint64_t* rl = ct_l + (size_t)i * w;
+    const uint64_t* rr = ct_r + (size_t)i * w;
+    const uint8_t* sky = view == 0 ? sky_l : sky_r;
+    const uint8_t* rs = sky ? sky + (size_t)i * w : nullptr;
+    float* out = cost + (size_t)view * h * w * d + (size_t)i * w * d + k;
+    const float sky_cost = k == 0 ? 0.0f : 999999.0f;
+    const int last = RecBox<WIN>::last_filtered(w);
+
+    RecBox<WIN> box;
+    box.reset();
+#pragma unroll 4
+    for (int j = 0; j < w; ++j) {
+        float c;
+        if (rs && __ldg(rs + j) == 255) {
+            c = sky_cost;  // src/Solver.cpp:165-179
+        } else if (view == 0) {
+            const int jr = max(j - shift, 0);  // src/Solver.cpp:185-189
+            c = (float)__popcll(__ldg(rl + j) ^ __ldg(rr + jr));
+        } else {
+            const int jl = min(j + shift, w - 1);  // src/Solver.cpp:239-243
+            c = (float)__popcll(__ldg(rl + jl) ^ __ldg(rr + j));
+        }
+        if (j < RecBox<WIN>::FIRST || j > last) out[(size_t)j * d] = c;  // unfiltered border columns
+        int pos;
+        float val;
+        if (box.feed(j, c, w, pos, val)) out[(size_t)pos * d] = val;
+    }
+}
+
+// src/Solver.cpp:333-368: the same recurrence down the rows, in place.  One thread per (column, d); rows are
+// read in batches of U so the loads of a batch are in flight together while the float chain advances.
+template <int WIN>
+__global__ void __launch_bounds__(256) vfilter_kernel(float* cost, int h, int w, int d) {
+    const size_t line = (size_t)w * d;
+    const size_t g = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= line) return;
+    float* base = cost + (size_t)blockIdx.y * h * line + g;
+    constexpr int U = 8;
+    RecBox<WIN> box;
+    box.reset();
+    for (int i0 = 0; i0 < h; i0 += U) {
+        float c[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (i0 + u < h) c[u] = base[(size_t)(i0 + u) * line];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (i0 + u < h) {
+                int pos;
+                float val;
+                if (box.feed(i0 + u, c[u], h, pos, val)) base[(size_t)pos * line] = val;
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// src/cost.cpp:4-30 (SAD) for every (pixel, d): with replicate-clamped window coordinates the sum separates
+// into a vertical sum per (clamped column, d) and a horizontal box over clamped columns.  One block handles a
+// row segment of SAD_TJ columns for all d: vertical sums (<= 9*255, uint16) go to shared memory, the horizontal
+// box slides over them there.  Integer sums are exact; the float result is sum / win_h / win_w like the reference.
+constexpr int SAD_TJ = 32;
+__global__ void __launch_bounds__(256) sad_volume_kernel(const uint8_t* __restrict__ img_l, const uint8_t* __restrict__ img_r,
+                                                         float* __restrict__ cost, int h, int w, int d, int win_h, int win_w,
+                                                         int scale) {
+    extern __shared__ uint16_t vs[];  // [(SAD_TJ + 2*rw)][d]
+    const int rh = win_h / 2, rw = win_w / 2;
+    const int i = blockIdx.y, j0 = blockIdx.x * SAD_TJ, view = blockIdx.z;
+    const int ncol = SAD_TJ + 2 * rw;
+    for (int t = threadIdx.x; t < ncol * d; t += blockDim.x) {
+        const int cx = t / d, k = t % d;
+        const int x = min(max(j0 + cx - rw, 0), w - 1);  // clamped window column (the reference clamps x_l / x_r)
+        int xl, xr;
+        if (view == 0) {
+            xl = x;
+            xr = max(x - k / scale, 0);
+        } else {
+            xr = x;
+            xl = min(x + k / scale, w - 1);
+        }
+        int acc = 0;
+        for (int a = -rh; a <= rh; ++a) {
+            const int y = min(max(i + a, 0), h - 1);
+            acc += abs((int)__ldg(img_l + (size_t)y * w + xl) - (int)__ldg(img_r + (size_t)y * w + xr));
+        }
+        vs[t] = (uint16_t)acc;
+    }
+    __syncthreads();
+    float* out = cost + ((size_t)view * h + i) * (size_t)w * d;
+    for (int t = threadIdx.x; t < SAD_TJ * d; t += blockDim.x) {
+        const int cj = t / d, k = t % d;
+        const int j = j0 + cj;
+        if (j >= w) continue;
+        int acc = 0;
+        for (int b = 0; b <= 2 * rw; ++b) acc += vs[(cj + b) * d + k];
+        out[(size_t)j * d + k] = __fdiv_rn(__fdiv_rn((float)acc, (float)win_h), (float)win_w);
+    }
+}
+
+}  // namespace
+
+void launch_subsample(const uint8_t* src, size_t src_stride, int col_step, int row_step, uint8_t* dst, int ih, int iw,
+                      cudaStream_t st, LaunchCounter& lc) {
+    dim3 grid((iw + 255) / 256, ih);
+    subsample_kernel<<<grid, 256, 0, st>>>(src, src_stride, col_step, row_step, dst, ih, iw);
+    lc.note();
+}
+
+void launch_blur3(const uint8_t* src, uint8_t* dst, int h, int w, cudaStream_t st, LaunchCounter& lc) {
+    dim3 grid((w + 255) / 256, h, 2);
+    blur3_kernel<<<grid, 256, 0, st>>>(src, dst, h, w);
+    lc.note();
+}
+
+void launch_census(const uint8_t* img, uint64_t* table, int h, int w, int win_h, int win_w, cudaStream_t st,
+                   LaunchCounter& lc) {
+    const int rh = win_h / 2, rw = win_w / 2;
+    if (rh > CT_MAX_RH || rw > CT_MAX_RW || (2 * rh + 1) * (2 * rw + 1) - 1 > 64) {
+        lc.err = cudaErrorInvalidValue;
+        return;
+    }
+    dim3 grid((w + CT_TX - 1) / CT_TX, (h + CT_TY - 1) / CT_TY, 2);
+    census_kernel<<<grid, dim3(CT_TX, CT_TY), 0, st>>>(img, table, h, w, rh, rw);
+    lc.note();
+}
+
+void launch_hamming_hfilter(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r,
+                            float* cost, int views, int h, int w, int d, int scale, int win, cudaStream_t st,
+                            LaunchCounter& lc) {
+    dim3 grid((h * d + 127) / 128, views);
+    switch (win) {
+        case 5: hamming_hfilter_kernel<5><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale); break;
+        case 4: hamming_hfilter_kernel<4><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale); break;
+        case 3: hamming_hfilter_kernel<3><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale); break;
+        case 2: hamming_hfilter_kernel<2><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale); break;
+        case 1: hamming_hfilter_kernel<1><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale); break;
+        default: lc.err = cudaErrorInvalidValue; return;
+    }
+    lc.note();
+}
+
+void launch_vfilter(float* cost, int views, int h, int w, int d, int win, cudaStream_t st, LaunchCounter& lc) {
+    dim3 grid((unsigned)(((size_t)w * d + 255) / 256), views);
+    switch (win) {
+        case 5: vfilter_kernel<5><<<grid, 256, 0, st>>>(cost, h, w, d); break;
+        case 4: vfilter_kernel<4><<<grid, 256, 0, st>>>(cost, h, w, d); break;
+        case 3: vfilter_kernel<3><<<grid, 256, 0, st>>>(cost, h, w, d); break;
+        case 2: vfilter_kernel<2><<<grid, 256, 0, st>>>(cost, h, w, d); break;
+        case 1: vfilter_kernel<1><<<grid, 256, 0, st>>>(cost, h, w, d); break;
+        default: lc.err = cudaErrorInvalidValue; return;
+    }
+    lc.note();
+}
+
+void launch_sad_volume(const uint8_t* img_l, const uint8_t* img_r, float* cost, int views, int h, int w, int d, int win_h,
+                       int win_w, int scale, cudaStream_t st, LaunchCounter& lc) {
+    const int rw = win_w / 2;
+    const size_t smem = (size_t)(SAD_TJ + 2 * rw) * d * sizeof(uint16_t);
+    if (smem > 48 * 1024 || win_h > 257) {
+        lc.err = cudaErrorInvalidValue;
+        return;
+    }
+    dim3 grid((w + SAD_TJ - 1) / SAD_TJ, h, views);
+    sad_volume_kernel<<<grid, 256, smem, st>>>(img_l, img_r, cost, h, w, d, win_h, win_w, scale);
+    lc.note();
+}
+
+}  // namespace sgmb200

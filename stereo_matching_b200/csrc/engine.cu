@@ -1,0 +1,546 @@
+// engine.cu — the C ABI of include/sgm_b200.h: owns device volumes, pinned staging, the stream and the
+// per-frame kernel schedule.  Host side of the drop-in boundary for the reference's Solver / SGM / BM
+// classes (inc/Solver.h:23-70, src/SGM.cpp:32-834, src/BM.cpp:9-105).  No CPU compute path exists here:
+// every stage is a kernel from cost_kernels.cu / aggregate_kernels.cu / post_kernels.cu.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "../../include/sgm_b200.h"
+#include "kernels.h"
+
+using namespace sgmb200;
+
+struct sgm_engine {
+    sgm_params p;
+    int ih = 0, iw = 0, D = 0, views = 1;
+    size_t n = 0, N = 0;  // pixels, pixels * D (working resolution)
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[SGM_STAGE_COUNT + 1] = {};
+    bool timing = false, have_result = false, result_on_host = false, busy = false;
+    int launches = 0;
+    float stage_ms[SGM_STAGE_COUNT] = {};
+    size_t device_bytes = 0;
+    std::string err;
+
+    // device
+    uint8_t* d_in[2] = {nullptr, nullptr};   // full-resolution staging of the host inputs (dense)
+    uint8_t* d_sky[2] = {nullptr, nullptr};  // [n] each
+    uint8_t* d_img = nullptr;                // [2][n] working-resolution images
+    uint8_t* d_blur = nullptr;               // [2][n]
+    uint64_t* d_census = nullptr;            // [2][n]
+    float* d_cost = nullptr;                 // [views][N]
+    float* d_acc_a = nullptr;                // [views][N]
+    float* d_acc_b = nullptr;                // [views][N]
+    float* d_pathsum = nullptr;              // [views][N] (SGM_FLAG_KEEP_VOLUMES)
+    uint16_t* d_disp = nullptr;              // [2][n]
+    float* d_sub = nullptr;                  // [2][n]
+    float* d_lr = nullptr;                   // [n]
+    float* d_med = nullptr;                  // [n]
+    float* d_final = nullptr;                // [n]
+    int* d_label = nullptr;                  // [n]
+    int* d_area = nullptr;                   // [n]
+    // pinned host
+    uint8_t* h_in[2] = {nullptr, nullptr};
+    uint8_t* h_sky[2] = {nullptr, nullptr};
+    float* h_final = nullptr;
+};
+
+namespace {
+
+thread_local std::string g_create_error;
+
+int fail(sgm_engine* e, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (e)
+        e->err = buf;
+    else
+        g_create_error = buf;
+    return code;
+}
+
+#define CU_TRY(e, call)                                                                                   \
+    do {                                                                                                  \
+        cudaError_t _c = (call);                                                                          \
+        if (_c != cudaSuccess) return fail((e), SGM_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(_c));   \
+    } while (0)
+
+template <typename T>
+cudaError_t dev_alloc(sgm_engine* e, T** p, size_t count) {
+    cudaError_t c = cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T));
+    if (c == cudaSuccess) e->device_bytes += count * sizeof(T);
+    return c;
+}
+
+void release(sgm_engine* e) {
+    if (!e) return;
+    cudaSetDevice(e->p.device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    for (int v = 0; v < 2; ++v) {
+        cudaFree(e->d_in[v]);
+        cudaFree(e->d_sky[v]);
+        cudaFreeHost(e->h_in[v]);
+        cudaFreeHost(e->h_sky[v]);
+    }
+    cudaFree(e->d_img);
+    cudaFree(e->d_blur);
+    cudaFree(e->d_census);
+    cudaFree(e->d_cost);
+    cudaFree(e->d_acc_a);
+    cudaFree(e->d_acc_b);
+    cudaFree(e->d_pathsum);
+    cudaFree(e->d_disp);
+    cudaFree(e->d_sub);
+    cudaFree(e->d_lr);
+    cudaFree(e->d_med);
+    cudaFree(e->d_final);
+    cudaFree(e->d_label);
+    cudaFree(e->d_area);
+    cudaFreeHost(e->h_final);
+    for (auto& ev : e->ev)
+        if (ev) cudaEventDestroy(ev);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+}  // namespace
+
+extern "C" {
+
+int sgm_abi_version(void) { return SGM_B200_ABI_VERSION; }
+
+void sgm_default_params(sgm_params* p, int height, int width, int scale, int max_disp, int algo) {
+    if (!p) return;
+    std::memset(p, 0, sizeof(*p));
+    p->height = height;
+    p->width = width;
+    p->scale = scale;
+    p->max_disp = max_disp;
+    p->algo = algo;
+    p->paths = 8;            // inc/SGM.h:7
+    p->P1 = 10;              // src/SGM.cpp:27
+    p->P2 = 100;             // src/SGM.cpp:28
+    p->census_h = 7;         // inc/Solver.h:10
+    p->census_w = 9;         // inc/Solver.h:11
+    p->box_h = 3;            // inc/Solver.h:12
+    p->box_w = 5;            // inc/Solver.h:13
+    p->unique_ratio = 0.7f;  // inc/Solver.h:14
+    p->lr_thresh = 1.0f;     // inc/Solver.h:16
+    p->median_h = 5;         // inc/Solver.h:17
+    p->median_w = 5;         // inc/Solver.h:18
+    p->speckle_size = 1000;  // inc/Solver.h:19
+    p->speckle_dis = 2;      // inc/Solver.h:20
+    p->sad_h = 9;
+    p->sad_w = 9;
+    p->device = 0;
+    p->flags = 0;
+}
+
+const char* sgm_last_error(const sgm_engine* e) { return e ? e->err.c_str() : g_create_error.c_str(); }
+
+int sgm_create(sgm_engine** out, const sgm_params* params) {
+    if (!out || !params) return fail(nullptr, SGM_ERR_INVALID, "sgm_create: null argument");
+    *out = nullptr;
+    const sgm_params& p = *params;
+    // src/Solver.cpp:6-10 asserts; here they are error codes
+    if (p.height <= 0 || p.width <= 0 || p.scale <= 0 || p.max_disp <= 0)
+        return fail(nullptr, SGM_ERR_INVALID, "h, w, scale, max_disp must be positive");
+    if (p.scale != 1 && p.scale != 2) return fail(nullptr, SGM_ERR_INVALID, "scale must be 1 or 2");
+    if (p.max_disp != 32 && p.max_disp != 64 && p.max_disp != 128 && p.max_disp != 256)
+        return fail(nullptr, SGM_ERR_UNSUPPORTED, "max_disp must be 32, 64, 128 or 256");
+    if (p.algo != SGM_ALGO_SGM && p.algo != SGM_ALGO_BM && p.algo != SGM_ALGO_BM_SAD)
+        return fail(nullptr, SGM_ERR_INVALID, "unknown algo %d", p.algo);
+    if (p.paths != 4 && p.paths != 8) return fail(nullptr, SGM_ERR_INVALID, "paths must be 4 or 8");
+    const int ih = p.height / p.scale, iw = p.width / p.scale;
+    const int bw = p.box_w / p.scale, bh = p.box_h / p.scale;
+    if (ih < 16 || iw < 16) return fail(nullptr, SGM_ERR_INVALID, "working image %dx%d is smaller than 16x16", iw, ih);
+    if (bw < 1 || bw > 5 || bh < 1 || bh > 5) return fail(nullptr, SGM_ERR_UNSUPPORTED, "box window / scale must be in 1..5");
+    if (!((p.median_h == 5 && p.median_w == 5) || (p.median_h == 3 && p.median_w == 3)))
+        return fail(nullptr, SGM_ERR_UNSUPPORTED, "median window must be 5x5 or 3x3");
+    if (p.algo != SGM_ALGO_BM_SAD) {
+        const int ch = p.census_h / p.scale, cw = p.census_w / p.scale;
+        if (ch / 2 > 3 || cw / 2 > 4 || ch < 1 || cw < 1)
+            return fail(nullptr, SGM_ERR_UNSUPPORTED, "census window / scale must fit 7x9");
+    } else {
+        const int sh = p.sad_h / p.scale, sw = p.sad_w / p.scale;
+        if (sh < 1 || sw < 1 || sh > 31 || sw > 31) return fail(nullptr, SGM_ERR_UNSUPPORTED, "SAD window / scale must be in 1..31");
+        if ((size_t)(32 + 2 * (sw / 2)) * p.max_disp * 2 > 48 * 1024)
+            return fail(nullptr, SGM_ERR_UNSUPPORTED, "SAD window too wide for this max_disp");
+    }
+    int ndev = 0;
+    cudaError_t c = cudaGetDeviceCount(&ndev);
+    if (c != cudaSuccess || ndev <= 0)
+        return fail(nullptr, SGM_ERR_CUDA, "no CUDA device (%s): this engine has no CPU path",
+                    c != cudaSuccess ? cudaGetErrorString(c) : "device count 0");
+    if (p.device < 0 || p.device >= ndev) return fail(nullptr, SGM_ERR_INVALID, "device %d out of range (0..%d)", p.device, ndev - 1);
+
+    sgm_engine* e = new (std::nothrow) sgm_engine();
+    if (!e) return fail(nullptr, SGM_ERR_NOMEM, "out of host memory");
+    e->p = p;
+    e->ih = ih;
+    e->iw = iw;
+    e->D = p.max_disp;
+    e->views = p.algo == SGM_ALGO_BM ? 1 : 2;
+    e->n = (size_t)ih * iw;
+    e->N = e->n * e->D;
+    e->timing = (p.flags & SGM_FLAG_STAGE_TIMING) != 0;
+    const size_t full = (size_t)p.height * p.width;
+    bool ok = cudaSetDevice(p.device) == cudaSuccess;
+    ok = ok && cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess;
+    for (int k = 0; ok && k <= SGM_STAGE_COUNT; ++k) ok = cudaEventCreate(&e->ev[k]) == cudaSuccess;
+    for (int v = 0; ok && v < 2; ++v) {
+        ok = ok && dev_alloc(e, &e->d_in[v], full) == cudaSuccess;
+        ok = ok && dev_alloc(e, &e->d_sky[v], e->n) == cudaSuccess;
+        ok = ok && cudaMallocHost(reinterpret_cast<void**>(&e->h_in[v]), full) == cudaSuccess;
+        ok = ok && cudaMallocHost(reinterpret_cast<void**>(&e->h_sky[v]), e->n) == cudaSuccess;
+    }
+    ok = ok && dev_alloc(e, &e->d_img, 2 * e->n) == cudaSuccess;
+    ok = ok && dev_alloc(e, &e->d_blur, 2 * e->n) == cudaSuccess;
+    ok = ok && dev_alloc(e, &e->d_census, 2 * e->n) == cudaSuccess;
+    ok = ok && dev_alloc(e, &e->d_cost, e->views * e->N) == cudaSuccess;
+    if (p.algo == SGM_ALGO_SGM) {
+        ok = ok && dev_alloc(e, &e->d_acc_a, e->views * e->N) == cudaSuccess;
+        if (p.paths == 8) ok = ok && dev_alloc(e, &e->d_acc_b, e->views * e->N) == cudaSuccess;
+        if (p.flags & SGM_FLAG_KEEP_VOLUMES) ok = ok && dev_alloc(e, &e->d_pathsum, e->views * e->N) == cudaSuccess;
+    }
+    ok = ok && dev_alloc(e, &e->d_disp, 2 * e->n) == cudaSuccess;
+    ok = ok && dev_alloc(e, &e->d_sub, 2 * e->n) == cudaSuccess;
+    ok = ok && dev_alloc(e, &e->d_lr, e->n) == cudaSuccess;
+    ok = ok && dev_alloc(e, &e->d_med, e->n) == cudaSuccess;
+    ok = ok && dev_alloc(e, &e->d_final, e->n) == cudaSuccess;
+    ok = ok && dev_alloc(e, &e->d_label, e->n) == cudaSuccess;
+    ok = ok && dev_alloc(e, &e->d_area, e->n) == cudaSuccess;
+    ok = ok && cudaMallocHost(reinterpret_cast<void**>(&e->h_final), e->n * sizeof(float)) == cudaSuccess;
+    if (!ok) {
+        cudaError_t last = cudaGetLastError();
+        fail(nullptr, last == cudaErrorMemoryAllocation ? SGM_ERR_NOMEM : SGM_ERR_CUDA, "sgm_create: allocation failed (%s)",
+             cudaGetErrorString(last));
+        release(e);
+        return last == cudaErrorMemoryAllocation ? SGM_ERR_NOMEM : SGM_ERR_CUDA;
+    }
+    *out = e;
+    return SGM_OK;
+}
+
+void sgm_destroy(sgm_engine* e) { release(e); }
+
+}  // extern "C"
+
+namespace {
+
+// Queues every kernel of one frame on the engine's stream.  left / right are device pointers to
+// full-resolution 8-bit images; sky masks (nullable) are dense device buffers at working resolution.
+int run_frame(sgm_engine* e, const uint8_t* left, size_t lstride, const uint8_t* right, size_t rstride, const uint8_t* sky_l,
+              const uint8_t* sky_r, LaunchCounter& lc) {
+    const sgm_params& p = e->p;
+    const int h = e->ih, w = e->iw, D = e->D, s = p.scale;
+    cudaStream_t st = e->stream;
+    const bool is_bm = p.algo != SGM_ALGO_SGM;
+
+    // ---- cost stage ----
+    if (e->timing) cudaEventRecord(e->ev[SGM_STAGE_COST], st);
+    const int row_step = is_bm ? 1 : s;  // src/BM.cpp:23-24 reads source row i, src/SGM.cpp:46-47 row i*scale
+    launch_subsample(left, lstride, s, row_step, e->d_img, h, w, st, lc);
+    launch_subsample(right, rstride, s, row_step, e->d_img + e->n, h, w, st, lc);
+    if (p.algo == SGM_ALGO_BM_SAD) {
+        launch_sad_volume(e->d_img, e->d_img + e->n, e->d_cost, e->views, h, w, D, p.sad_h / s, p.sad_w / s, s, st, lc);
+    } else {
+        launch_blur3(e->d_img, e->d_blur, h, w, st, lc);                                   // src/Solver.cpp:124-125
+        launch_census(e->d_blur, e->d_census, h, w, p.census_h / s, p.census_w / s, st, lc);  // :127-139
+        launch_hamming_hfilter(e->d_census, e->d_census + e->n, sky_l, sky_r, e->d_cost, e->views, h, w, D, s, p.box_w / s, st,
+                               lc);                                                          // :143-248, :296-330
+        launch_vfilter(e->d_cost, e->views, h, w, D, p.box_h / s, st, lc);                  // :333-368
+    }
+
+    // ---- aggregation / selection ----
+    if (e->timing) cudaEventRecord(e->ev[SGM_STAGE_AGGREGATE], st);
+    if (p.algo == SGM_ALGO_SGM) {
+        AggregateArgs a;
+        a.cost = e->d_cost;
+        a.acc_a = e->d_acc_a;
+        a.acc_b = e->d_acc_b;
+        a.pathsum = e->d_pathsum;
+        a.disp = e->d_disp;
+        a.subpixel = e->d_sub;
+        a.views = e->views;
+        a.h = h;
+        a.w = w;
+        a.d = D;
+        a.paths = p.paths;
+        a.P1 = (float)p.P1;
+        a.P2 = (float)p.P2;
+        a.unique_ratio = p.unique_ratio;
+        a.min_gap = 1;
+        launch_aggregate(a, st, lc);
+    } else {
+        // src/BM.cpp:52-91; census-BM gets compute_subpixel on the filtered cost, SAD-BM keeps integers
+        launch_wta(e->d_cost, e->d_disp, e->d_sub, e->views, h, w, D, p.unique_ratio, 2, p.algo == SGM_ALGO_BM ? 1 : 0, st, lc);
+    }
+
+    // ---- post stage ----
+    if (e->timing) cudaEventRecord(e->ev[SGM_STAGE_POST], st);
+    if (e->views == 2) {
+        launch_lr_check(e->d_sub, e->d_sub + e->n, e->d_lr, e->d_med, h, w, D, s, p.lr_thresh, st, lc);  // src/SGM.cpp:803-818
+    } else {
+        cudaMemcpyAsync(e->d_lr, e->d_sub, e->n * sizeof(float), cudaMemcpyDeviceToDevice, st);
+        cudaMemcpyAsync(e->d_med, e->d_sub, e->n * sizeof(float), cudaMemcpyDeviceToDevice, st);
+    }
+    launch_median_fill(e->d_lr, e->d_med, h, w, D, p.median_h, p.median_w, st, lc);  // src/Solver.cpp:604-630
+    launch_speckle(e->d_med, e->d_final, e->d_label, e->d_area, h, w, (float)(D + 1), p.speckle_size / s, (float)p.speckle_dis, st,
+                   lc);                                                              // src/Solver.cpp:634
+    if (e->timing) cudaEventRecord(e->ev[SGM_STAGE_DOWNLOAD], st);
+    if (lc.err != cudaSuccess) return fail(e, SGM_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(lc.err));
+    return SGM_OK;
+}
+
+int check_images(sgm_engine* e, const void* left, size_t ls, const void* right, size_t rs, const void* sl, size_t sls, const void* sr,
+                 size_t srs) {
+    if (!e) return SGM_ERR_INVALID;
+    if (!left || !right) return fail(e, SGM_ERR_INVALID, "left / right image is null");
+    if (ls < (size_t)e->p.width || rs < (size_t)e->p.width) return fail(e, SGM_ERR_INVALID, "image stride smaller than width");
+    if ((sl && sls < (size_t)e->iw) || (sr && srs < (size_t)e->iw)) return fail(e, SGM_ERR_INVALID, "sky mask stride smaller than width");
+    if (e->busy) return fail(e, SGM_ERR_STATE, "a frame is already in flight on this handle: call sgm_wait first");
+    return SGM_OK;
+}
+
+void pack_rows(uint8_t* dst, const uint8_t* src, size_t stride, int rows, int cols) {
+    if (stride == (size_t)cols) {
+        std::memcpy(dst, src, (size_t)rows * cols);
+        return;
+    }
+    for (int r = 0; r < rows; ++r) std::memcpy(dst + (size_t)r * cols, src + (size_t)r * stride, cols);
+}
+
+}  // namespace
+
+extern "C" {
+
+int sgm_enqueue(sgm_engine* e, const uint8_t* left, size_t ls, const uint8_t* right, size_t rs, const uint8_t* sky_l, size_t sls,
+                const uint8_t* sky_r, size_t srs) {
+    int rc = check_images(e, left, ls, right, rs, sky_l, sls, sky_r, srs);
+    if (rc != SGM_OK) return rc;
+    CU_TRY(e, cudaSetDevice(e->p.device));
+    const int H = e->p.height, W = e->p.width;
+    cudaStream_t st = e->stream;
+    // pinned staging, then async H2D on the engine's stream
+    pack_rows(e->h_in[0], left, ls, H, W);
+    pack_rows(e->h_in[1], right, rs, H, W);
+    if (sky_l) pack_rows(e->h_sky[0], sky_l, sls, e->ih, e->iw);
+    if (sky_r) pack_rows(e->h_sky[1], sky_r, srs, e->ih, e->iw);
+    cudaEventRecord(e->ev[SGM_STAGE_UPLOAD], st);
+    CU_TRY(e, cudaMemcpyAsync(e->d_in[0], e->h_in[0], (size_t)H * W, cudaMemcpyHostToDevice, st));
+    CU_TRY(e, cudaMemcpyAsync(e->d_in[1], e->h_in[1], (size_t)H * W, cudaMemcpyHostToDevice, st));
+    if (sky_l) CU_TRY(e, cudaMemcpyAsync(e->d_sky[0], e->h_sky[0], e->n, cudaMemcpyHostToDevice, st));
+    if (sky_r) CU_TRY(e, cudaMemcpyAsync(e->d_sky[1], e->h_sky[1], e->n, cudaMemcpyHostToDevice, st));
+    LaunchCounter lc;
+    rc = run_frame(e, e->d_in[0], W, e->d_in[1], W, sky_l ? e->d_sky[0] : nullptr, sky_r ? e->d_sky[1] : nullptr, lc);
+    e->launches = lc.launches;
+    if (rc != SGM_OK) return rc;
+    CU_TRY(e, cudaMemcpyAsync(e->h_final, e->d_final, e->n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    cudaEventRecord(e->ev[SGM_STAGE_COUNT], st);
+    e->busy = true;
+    e->result_on_host = true;
+    return SGM_OK;
+}
+
+int sgm_enqueue_device(sgm_engine* e, const void* left, size_t ls, const void* right, size_t rs, const void* sky_l, size_t sls,
+                       const void* sky_r, size_t srs) {
+    int rc = check_images(e, left, ls, right, rs, sky_l, sls, sky_r, srs);
+    if (rc != SGM_OK) return rc;
+    CU_TRY(e, cudaSetDevice(e->p.device));
+    cudaStream_t st = e->stream;
+    const uint8_t* sl = static_cast<const uint8_t*>(sky_l);
+    const uint8_t* sr = static_cast<const uint8_t*>(sky_r);
+    cudaEventRecord(e->ev[SGM_STAGE_UPLOAD], st);
+    if (sl && sls != (size_t)e->iw) {  // densify a pitched mask
+        CU_TRY(e, cudaMemcpy2DAsync(e->d_sky[0], e->iw, sl, sls, e->iw, e->ih, cudaMemcpyDeviceToDevice, st));
+        sl = e->d_sky[0];
+    }
+    if (sr && srs != (size_t)e->iw) {
+        CU_TRY(e, cudaMemcpy2DAsync(e->d_sky[1], e->iw, sr, srs, e->iw, e->ih, cudaMemcpyDeviceToDevice, st));
+        sr = e->d_sky[1];
+    }
+    LaunchCounter lc;
+    rc = run_frame(e, static_cast<const uint8_t*>(left), ls, static_cast<const uint8_t*>(right), rs, sl, sr, lc);
+    e->launches = lc.launches;
+    if (rc != SGM_OK) return rc;
+    cudaEventRecord(e->ev[SGM_STAGE_COUNT], st);
+    e->busy = true;
+    e->result_on_host = false;
+    return SGM_OK;
+}
+
+int sgm_wait(sgm_engine* e) {
+    if (!e) return SGM_ERR_INVALID;
+    if (!e->busy) return SGM_OK;
+    CU_TRY(e, cudaSetDevice(e->p.device));
+    cudaError_t c = cudaStreamSynchronize(e->stream);
+    e->busy = false;
+    if (c != cudaSuccess) return fail(e, SGM_ERR_CUDA, "frame failed: %s", cudaGetErrorString(c));
+    e->have_result = true;
+    if (e->timing) {
+        for (int k = 0; k < SGM_STAGE_COUNT; ++k) {
+            float ms = 0.f;
+            const int nxt = k + 1 == SGM_STAGE_COUNT ? SGM_STAGE_COUNT : k + 1;
+            if (cudaEventElapsedTime(&ms, e->ev[k], e->ev[nxt]) != cudaSuccess) ms = -1.f;
+            e->stage_ms[k] = ms;
+        }
+        (void)cudaGetLastError();
+    }
+    return SGM_OK;
+}
+
+int sgm_process(sgm_engine* e, const uint8_t* left, size_t ls, const uint8_t* right, size_t rs, const uint8_t* sky_l, size_t sls,
+                const uint8_t* sky_r, size_t srs) {
+    int rc = sgm_enqueue(e, left, ls, right, rs, sky_l, sls, sky_r, srs);
+    if (rc != SGM_OK) return rc;
+    return sgm_wait(e);
+}
+
+static int ready(sgm_engine* e) {
+    if (!e) return SGM_ERR_INVALID;
+    if (e->busy) {
+        int rc = sgm_wait(e);
+        if (rc != SGM_OK) return rc;
+    }
+    if (!e->have_result) return fail(e, SGM_ERR_STATE, "no frame has been processed yet");
+    if (cudaSetDevice(e->p.device) != cudaSuccess) return fail(e, SGM_ERR_CUDA, "cudaSetDevice failed");
+    return SGM_OK;
+}
+
+int sgm_get_disparity_f32(sgm_engine* e, float* dst, size_t dst_stride) {
+    int rc = ready(e);
+    if (rc != SGM_OK) return rc;
+    if (!dst || dst_stride < e->iw * sizeof(float)) return fail(e, SGM_ERR_INVALID, "bad destination");
+    if (e->result_on_host) {
+        for (int r = 0; r < e->ih; ++r)
+            std::memcpy(reinterpret_cast<char*>(dst) + (size_t)r * dst_stride, e->h_final + (size_t)r * e->iw, e->iw * sizeof(float));
+        return SGM_OK;
+    }
+    CU_TRY(e, cudaMemcpy2D(dst, dst_stride, e->d_final, e->iw * sizeof(float), e->iw * sizeof(float), e->ih, cudaMemcpyDeviceToHost));
+    return SGM_OK;
+}
+
+int sgm_get_disparity_u16(sgm_engine* e, int view, uint16_t* dst, size_t dst_stride) {
+    int rc = ready(e);
+    if (rc != SGM_OK) return rc;
+    if (!dst || dst_stride < e->iw * sizeof(uint16_t) || view < 0 || view >= e->views) return fail(e, SGM_ERR_INVALID, "bad destination / view");
+    CU_TRY(e, cudaMemcpy2D(dst, dst_stride, e->d_disp + (size_t)view * e->n, e->iw * sizeof(uint16_t), e->iw * sizeof(uint16_t), e->ih,
+                           cudaMemcpyDeviceToHost));
+    return SGM_OK;
+}
+
+int sgm_get_disparity_u8(sgm_engine* e, int view, uint8_t* dst, size_t dst_stride) {
+    int rc = ready(e);
+    if (rc != SGM_OK) return rc;
+    if (e->D > 128) return fail(e, SGM_ERR_UNSUPPORTED, "8-bit disparity needs max_disp <= 128 (invalid = D+1 must fit a byte)");
+    if (!dst || dst_stride < (size_t)e->iw || view < 0 || view >= e->views) return fail(e, SGM_ERR_INVALID, "bad destination / view");
+    uint16_t* tmp = static_cast<uint16_t*>(std::malloc(e->n * sizeof(uint16_t)));
+    if (!tmp) return fail(e, SGM_ERR_NOMEM, "out of host memory");
+    cudaError_t c = cudaMemcpy(tmp, e->d_disp + (size_t)view * e->n, e->n * sizeof(uint16_t), cudaMemcpyDeviceToHost);
+    if (c == cudaSuccess)
+        for (int r = 0; r < e->ih; ++r)
+            for (int k = 0; k < e->iw; ++k) dst[(size_t)r * dst_stride + k] = (uint8_t)tmp[(size_t)r * e->iw + k];  // uchar Mat, src/Solver.cpp:18-19
+    std::free(tmp);
+    if (c != cudaSuccess) return fail(e, SGM_ERR_CUDA, "cudaMemcpy: %s", cudaGetErrorString(c));
+    return SGM_OK;
+}
+
+const float* sgm_disparity_device(sgm_engine* e) { return e ? e->d_final : nullptr; }
+
+size_t sgm_tap_bytes(const sgm_engine* e, int which) {
+    if (!e) return 0;
+    switch (which) {
+        case SGM_TAP_CENSUS: return e->n * sizeof(uint64_t);
+        case SGM_TAP_COST:
+        case SGM_TAP_PATHSUM: return e->N * sizeof(float);
+        case SGM_TAP_DISP: return e->n * sizeof(uint16_t);
+        case SGM_TAP_SUBPIXEL:
+        case SGM_TAP_LR:
+        case SGM_TAP_MEDIAN:
+        case SGM_TAP_FINAL: return e->n * sizeof(float);
+        case SGM_TAP_BLUR: return e->n;
+        default: return 0;
+    }
+}
+
+int sgm_get_tap(sgm_engine* e, int which, int view, void* dst, size_t bytes) {
+    int rc = ready(e);
+    if (rc != SGM_OK) return rc;
+    if (!dst || bytes != sgm_tap_bytes(e, which) || bytes == 0) return fail(e, SGM_ERR_INVALID, "tap %d: bad destination size", which);
+    if (view < 0 || view > 1) return fail(e, SGM_ERR_INVALID, "view must be 0 or 1");
+    const void* src = nullptr;
+    switch (which) {
+        case SGM_TAP_CENSUS: src = e->p.algo == SGM_ALGO_BM_SAD ? nullptr : e->d_census + (size_t)view * e->n; break;
+        case SGM_TAP_BLUR: src = e->p.algo == SGM_ALGO_BM_SAD ? nullptr : e->d_blur + (size_t)view * e->n; break;
+        case SGM_TAP_COST:
+            // SGM mode: acc/cost buffers are scratch but the filtered cost volume itself is never overwritten
+            src = view < e->views ? e->d_cost + (size_t)view * e->N : nullptr;
+            break;
+        case SGM_TAP_PATHSUM: src = (e->d_pathsum && view < e->views) ? e->d_pathsum + (size_t)view * e->N : nullptr; break;
+        case SGM_TAP_DISP: src = view < e->views ? e->d_disp + (size_t)view * e->n : nullptr; break;
+        case SGM_TAP_SUBPIXEL: src = view < e->views ? e->d_sub + (size_t)view * e->n : nullptr; break;
+        case SGM_TAP_LR: src = view == 0 ? e->d_lr : nullptr; break;
+        case SGM_TAP_MEDIAN: src = view == 0 ? e->d_med : nullptr; break;
+        case SGM_TAP_FINAL: src = view == 0 ? e->d_final : nullptr; break;
+        default: break;
+    }
+    if (!src) return fail(e, SGM_ERR_STATE, "tap %d / view %d is not available in this mode", which, view);
+    CU_TRY(e, cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
+    return SGM_OK;
+}
+
+int sgm_get_size(const sgm_engine* e, int* out_h, int* out_w, int* out_d) {
+    if (!e) return SGM_ERR_INVALID;
+    if (out_h) *out_h = e->ih;
+    if (out_w) *out_w = e->iw;
+    if (out_d) *out_d = e->D;
+    return SGM_OK;
+}
+int sgm_get_launch_count(const sgm_engine* e) { return e ? e->launches : -1; }
+int sgm_get_stage_ms(sgm_engine* e, float* ms, int count) {
+    int rc = ready(e);
+    if (rc != SGM_OK) return rc;
+    if (!e->timing) return fail(e, SGM_ERR_STATE, "engine was created without SGM_FLAG_STAGE_TIMING");
+    for (int k = 0; k < count && k < SGM_STAGE_COUNT; ++k) ms[k] = e->stage_ms[k];
+    return SGM_OK;
+}
+void* sgm_get_stream(sgm_engine* e) { return e ? (void*)e->stream : nullptr; }
+size_t sgm_device_bytes(const sgm_engine* e) { return e ? e->device_bytes : 0; }
+
+int sgm_cost_volume_sad(int device, const uint8_t* left, const uint8_t* right, int height, int width, int max_disp, int win_h, int win_w,
+                        int scale, float* out) {
+    if (!left || !right || !out || height <= 0 || width <= 0 || max_disp <= 0 || scale <= 0 || win_h <= 0 || win_w <= 0)
+        return fail(nullptr, SGM_ERR_INVALID, "sgm_cost_volume_sad: bad argument");
+    if ((size_t)(32 + 2 * (win_w / 2)) * max_disp * 2 > 48 * 1024 || win_h > 257)
+        return fail(nullptr, SGM_ERR_UNSUPPORTED, "sgm_cost_volume_sad: window too large for this max_disp");
+    if (cudaSetDevice(device) != cudaSuccess) return fail(nullptr, SGM_ERR_CUDA, "no CUDA device %d: this engine has no CPU path", device);
+    const size_t n = (size_t)height * width, N = n * max_disp;
+    uint8_t* d_img = nullptr;
+    float* d_cost = nullptr;
+    cudaError_t c = cudaMalloc(reinterpret_cast<void**>(&d_img), 2 * n);
+    if (c == cudaSuccess) c = cudaMalloc(reinterpret_cast<void**>(&d_cost), N * sizeof(float));
+    if (c == cudaSuccess) c = cudaMemcpy(d_img, left, n, cudaMemcpyHostToDevice);
+    if (c == cudaSuccess) c = cudaMemcpy(d_img + n, right, n, cudaMemcpyHostToDevice);
+    LaunchCounter lc;
+    if (c == cudaSuccess) {
+        launch_sad_volume(d_img, d_img + n, d_cost, 1, height, width, max_disp, win_h, win_w, scale, nullptr, lc);
+        c = lc.err;
+    }
+    if (c == cudaSuccess) c = cudaMemcpy(out, d_cost, N * sizeof(float), cudaMemcpyDeviceToHost);
+    cudaFree(d_img);
+    cudaFree(d_cost);
+    if (c != cudaSuccess) return fail(nullptr, SGM_ERR_CUDA, "sgm_cost_volume_sad: %s", cudaGetErrorString(c));
+    return SGM_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,76 @@
+// kernels.h — host-side launchers of the sm_100a stereo kernels (internal to libsgm_b200.so).
+// Each launcher cites the reference stage it replaces; every launch goes through `count` so the
+// engine can report how many kernels a frame took.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace sgmb200 {
+
+struct LaunchCounter {
+    int launches = 0;
+    cudaError_t err = cudaSuccess;
+    void note() {
+        ++launches;
+        cudaError_t e = cudaGetLastError();
+        if (err == cudaSuccess && e != cudaSuccess) err = e;
+    }
+};
+
+// ---- cost stage (cost_kernels.cu) ------------------------------------------------------------
+// src/SGM.cpp:40-56 / src/BM.cpp:17-33: nearest-neighbour decimation (row_step = scale for SGM, 1 for BM).
+void launch_subsample(const uint8_t* src, size_t src_stride, int col_step, int row_step, uint8_t* dst, int ih, int iw,
+                      cudaStream_t st, LaunchCounter& lc);
+// src/Solver.cpp:124-125: 3x3 Gaussian (sigma 2, 1) in OpenCV's 8-bit fixed point; both images in one launch.
+void launch_blur3(const uint8_t* src /*[2][h*w]*/, uint8_t* dst /*[2][h*w]*/, int h, int w, cudaStream_t st,
+                  LaunchCounter& lc);
+// src/cost.cpp:99-129 (CT_pts) for every pixel of both images in one launch.
+void launch_census(const uint8_t* img /*[2][h*w]*/, uint64_t* table /*[2][h*w]*/, int h, int w, int win_h, int win_w,
+                   cudaStream_t st, LaunchCounter& lc);
+// src/Solver.cpp:143-248 fused with cost_horizontal_filter (:296-330): view v of `cost` (stride n*d floats) gets
+// the Hamming volume of view v, recursively box-filtered along j.  sky[v] nullable.
+void launch_hamming_hfilter(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r,
+                            float* cost, int views, int h, int w, int d, int scale, int win, cudaStream_t st,
+                            LaunchCounter& lc);
+// src/Solver.cpp:333-368 in place on `views` volumes.
+void launch_vfilter(float* cost, int views, int h, int w, int d, int win, cudaStream_t st, LaunchCounter& lc);
+// src/cost.cpp:4-30 (SAD) for every (pixel, d) of `views` views (view 1 = right view by symmetry).
+void launch_sad_volume(const uint8_t* img_l, const uint8_t* img_r, float* cost, int views, int h, int w, int d,
+                       int win_h, int win_w, int scale, cudaStream_t st, LaunchCounter& lc);
+
+// ---- aggregation (aggregate_kernels.cu) ------------------------------------------------------
+struct AggregateArgs {
+    const float* cost;  // [views][n*d]   filtered cost volume C
+    float* acc_a;       // [views][n*d]   scratch: ((L1+L2)+L3)+L4
+    float* acc_b;       // [views][n*d]   scratch: ((L5+L6)+L7)
+    float* pathsum;     // [views][n*d]   optional: S written out (debug tap), else nullptr
+    uint16_t* disp;     // [views][n]
+    float* subpixel;    // [views][n]
+    int views, h, w, d, paths;
+    float P1, P2, unique_ratio;
+    int min_gap;        // 1 for SGM (src/SGM.cpp:409), 2 for BM (src/BM.cpp:82)
+};
+// src/SGM.cpp:82-418 + compute_subpixel (src/Solver.cpp:569-597): the path recurrences, their sum in the
+// reference's association order, WTA, uniqueness and the sub-pixel parabola.
+void launch_aggregate(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc);
+// src/BM.cpp:52-91 (+ compute_subpixel when parabola != 0): WTA / uniqueness straight on a cost volume.
+void launch_wta(const float* vol, uint16_t* disp, float* subpixel, int views, int h, int w, int d, float unique_ratio,
+                int min_gap, int parabola, cudaStream_t st, LaunchCounter& lc);
+
+// ---- post stage (post_kernels.cu) --------------------------------------------------------------
+// src/SGM.cpp:803-818.
+// The checked image is written to both out_keep (tap) and out_work (the buffer the median then updates in place).
+void launch_lr_check(const float* left, const float* right, float* out_keep, float* out_work, int h, int w, int d,
+                     int scale, float thresh, cudaStream_t st, LaunchCounter& lc);
+// src/Solver.cpp:604-630, exact raster-order semantics through a wavefront.  `src` = read-only copy of the
+// image before filling, `f` = the image being filled in place (same content on entry).
+void launch_median_fill(const float* src, float* f, int h, int w, int d, int win_h, int win_w, cudaStream_t st,
+                        LaunchCounter& lc);
+// src/Solver.cpp:514-566 with serial semantics: f_out = f_in with small components set to `value`;
+// labels / area are n-int scratch buffers.
+void launch_speckle(const float* f_in, float* f_out, int* labels, int* area, int h, int w, float value, int max_size,
+                    float max_dis, cudaStream_t st, LaunchCounter& lc);
+
+}  // namespace sgmb200

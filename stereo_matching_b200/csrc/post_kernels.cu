@@ -1,0 +1,204 @@
+// post_kernels.cu — LR-consistency check, hole-filling median and speckle filter (sm_100a).
+//
+// Replaces src/SGM.cpp:803-818 and Solver::post_filter (src/Solver.cpp:600-635, speckle_filter_new
+// :514-566) of the reference, with the reference's serial (single-thread) semantics.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace sgmb200 {
+
+namespace {
+
+// src/SGM.cpp:803-818: for j >= dl: dr = right(i, int(j - dl/scale)); |dl - dr| > thresh -> dl = D+1.
+// Writes the result twice: `out_keep` (the LR tap) and `out_work` (the buffer the median updates in place).
+__global__ void lr_check_kernel(const float* __restrict__ left, const float* __restrict__ right, float* __restrict__ out_keep,
+                                float* __restrict__ out_work, int h, int w, int d, int scale, float thresh) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    if (j >= w) return;
+    const size_t p = (size_t)i * w + j;
+    float dl = left[p];
+    if ((float)j >= dl) {
+        const int jr = (int)__fsub_rn((float)j, __fdiv_rn(dl, (float)scale));
+        const float dr = right[(size_t)i * w + jr];
+        if (fabsf(__fsub_rn(dl, dr)) > thresh) dl = (float)(d + 1);
+    }
+    out_keep[p] = dl;
+    out_work[p] = dl;
+}
+
+// src/Solver.cpp:604-630.  The reference fills holes IN PLACE in raster order, so a pixel sees the fills of
+// earlier pixels in its window.  Pixel (i, j) depends on rows i-rh..i-1 up to column j+rw and on row i left
+// of j; the wavefront t = j + (rw+1)*i orders all of those strictly before it.  One block walks the
+// wavefront, one row per thread (rows strided over the block when h > blockDim).  `src` is the read-only
+// pre-filter image (a pixel is only ever written by its own step, so src tells whether it is a hole without
+// touching the buffer being updated); holes gather their window from `f` through L2 (__ldcg).
+template <int WH, int WW>
+__global__ void __launch_bounds__(1024) median_fill_kernel(const float* __restrict__ src, float* f, int h, int w, int d) {
+    constexpr int RH = WH / 2, RW = WW / 2, K = RW + 1, NWIN = WH * WW;
+    const float vmax = (float)(d - 1);
+    const int steps = (w - 1) + K * (h - 1) + 1;
+    for (int t = 0; t < steps; ++t) {
+        for (int i = threadIdx.x; i < h; i += blockDim.x) {
+            const int j = t - K * i;
+            if (j < RW || j >= w - RW || i < RH || i >= h - RH) continue;
+            if (__ldg(src + (size_t)i * w + j) <= vmax) continue;  // not a hole
+            int vals[NWIN];
+            int cnt = 0;
+#pragma unroll
+            for (int a = -RH; a <= RH; ++a)
+#pragma unroll
+                for (int b = -RW; b <= RW; ++b) {
+                    const float v = __ldcg(f + (size_t)(i + a) * w + (j + b));
+                    const bool ok = v <= vmax;
+                    vals[(a + RH) * WW + (b + RW)] = ok ? (int)v : 0x7fffffff;  // float -> int truncation (:619)
+                    cnt += ok ? 1 : 0;
+                }
+            if (cnt > NWIN / 2) {
+                // sorted[cnt / 2] by rank counting (ties broken by position): invalid entries sort last
+                const int want = cnt / 2;
+                int pick = 0;
+#pragma unroll
+                for (int x = 0; x < NWIN; ++x) {
+                    int rank = 0;
+#pragma unroll
+                    for (int y = 0; y < NWIN; ++y) rank += (vals[y] < vals[x] || (vals[y] == vals[x] && y < x)) ? 1 : 0;
+                    if (rank == want) pick = vals[x];
+                }
+                f[(size_t)i * w + j] = (float)pick;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ---- speckle filter: exact 4-connected components under |a - b| < max_dis (src/Solver.cpp:514-566) -----
+// Union-find with min-index roots.  Labels only ever decrease and always stay inside the component, so a
+// stale read merely costs extra hops.
+__device__ __forceinline__ int uf_root(const int* label, int x) {
+    while (true) {
+        const int p = __ldcg(label + x);
+        if (p == x) return x;
+        x = p;
+    }
+}
+__device__ __forceinline__ void uf_unite(int* label, int a, int b) {
+    while (true) {
+        a = uf_root(label, a);
+        b = uf_root(label, b);
+        if (a == b) return;
+        if (a < b) {
+            const int t = a;
+            a = b;
+            b = t;
+        }
+        const int old = atomicMin(label + a, b);  // a > b: hang root a under b
+        if (old == a) return;
+        a = old;  // a was no longer a root: keep merging from where it points now
+    }
+}
+
+// Pass 1: horizontal runs.  One warp per row; label = index of the first pixel of the maximal run of
+// horizontally linked pixels; area cleared.
+__global__ void speckle_rows_kernel(const float* __restrict__ f, int* __restrict__ label, int* __restrict__ area, int h, int w,
+                                    float max_dis) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= h) return;
+    const float* row = f + (size_t)i * w;
+    int carry = 0;  // start column of the run that reaches into this chunk
+    for (int j0 = 0; j0 < w; j0 += 32) {
+        const int j = j0 + lane;
+        bool starts = true;  // does a new run start at j?
+        if (j < w && j > 0) starts = !(fabsf(__fsub_rn(row[j], row[j - 1])) < max_dis);
+        if (j >= w) starts = true;
+        const unsigned m = __ballot_sync(FULL_MASK, starts);
+        const unsigned upto = m & (0xffffffffu >> (31 - lane));  // starts at lanes <= mine
+        const int start = upto ? j0 + (31 - __clz(upto)) : carry;
+        if (j < w) {
+            label[(size_t)i * w + j] = i * w + start;
+            area[(size_t)i * w + j] = 0;
+        }
+        // run reaching past this chunk starts at the last start flag of the chunk (or carries on)
+        carry = m ? j0 + (31 - __clz(m)) : carry;
+    }
+}
+
+// Pass 2: vertical links.  Redundant unions inside a pair of vertically linked runs are skipped: pixel j only
+// unites with the pixel below when its left neighbour does not already carry the same pair of runs down.
+__global__ void speckle_merge_kernel(const float* __restrict__ f, int* label, int h, int w, float max_dis) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    if (j >= w || i >= h - 1) return;
+    const size_t p = (size_t)i * w + j;
+    const float a = f[p], b = f[p + w];
+    if (!(fabsf(__fsub_rn(a, b)) < max_dis)) return;
+    if (j > 0) {
+        const float al = f[p - 1], bl = f[p + w - 1];
+        const bool same_pair = fabsf(__fsub_rn(al, bl)) < max_dis && fabsf(__fsub_rn(a, al)) < max_dis &&
+                               fabsf(__fsub_rn(b, bl)) < max_dis;
+        if (same_pair) return;
+    }
+    uf_unite(label, (int)p, (int)(p + w));
+}
+
+// Pass 3: flatten and count.  Lanes of a warp that share a root add once.
+__global__ void speckle_count_kernel(int* label, int* area, int n) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = p < n;
+    int root = -1 - (int)(threadIdx.x & 31);  // distinct dummy per dead lane
+    if (live) {
+        root = uf_root(label, p);
+        label[p] = root;
+    }
+    const unsigned peers = __match_any_sync(FULL_MASK, root);
+    if (live && (int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(area + root, __popc(peers));
+}
+
+// Pass 4: components of area <= max_size become `value` (:555-565).
+__global__ void speckle_apply_kernel(const float* __restrict__ f_in, float* __restrict__ f_out, const int* __restrict__ label,
+                                     const int* __restrict__ area, int n, float value, int max_size) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    f_out[p] = area[label[p]] <= max_size ? value : f_in[p];
+}
+
+}  // namespace
+
+void launch_lr_check(const float* left, const float* right, float* out_keep, float* out_work, int h, int w, int d, int scale,
+                     float thresh, cudaStream_t st, LaunchCounter& lc) {
+    dim3 grid((w + 255) / 256, h);
+    lr_check_kernel<<<grid, 256, 0, st>>>(left, right, out_keep, out_work, h, w, d, scale, thresh);
+    lc.note();
+}
+
+void launch_median_fill(const float* src, float* f, int h, int w, int d, int win_h, int win_w, cudaStream_t st,
+                        LaunchCounter& lc) {
+    int threads = ((h + 31) / 32) * 32;
+    if (threads > 1024) threads = 1024;
+    if (win_h == 5 && win_w == 5)
+        median_fill_kernel<5, 5><<<1, threads, 0, st>>>(src, f, h, w, d);
+    else if (win_h == 3 && win_w == 3)
+        median_fill_kernel<3, 3><<<1, threads, 0, st>>>(src, f, h, w, d);
+    else {
+        lc.err = cudaErrorInvalidValue;
+        return;
+    }
+    lc.note();
+}
+
+void launch_speckle(const float* f, float* f_out, int* labels, int* area, int h, int w, float value, int max_size,
+                    float max_dis, cudaStream_t st, LaunchCounter& lc) {
+    const int n = h * w;
+    speckle_rows_kernel<<<(h + 7) / 8, 256, 0, st>>>(f, labels, area, h, w, max_dis);
+    lc.note();
+    dim3 grid((w + 255) / 256, h);
+    speckle_merge_kernel<<<grid, 256, 0, st>>>(f, labels, h, w, max_dis);
+    lc.note();
+    speckle_count_kernel<<<(n + 255) / 256, 256, 0, st>>>(labels, area, n);
+    lc.note();
+    speckle_apply_kernel<<<(n + 255) / 256, 256, 0, st>>>(f, f_out, labels, area, n, value, max_size);
+    lc.note();
+}
+
+}  // namespace sgmb200

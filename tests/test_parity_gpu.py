@@ -1,0 +1,248 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI (stereo_matching_b200.capi ->
+libsgm_b200.so), against the oracle on the same seeded inputs.
+
+  * small / mid sizes: every stage tap bit-for-bit against the restatement (oracle/sgm_oracle.c) and,
+    where the compiled reference travelled (oracle/_ref), against the reference itself;
+  * BASELINE.json's KITTI-size configs: against the golden hashes the reference produced
+    (tests/golden/kat_hashes.json) — no oracle needed at run time;
+  * sizes the reference cannot run (D=256, 1080p): against the widened restatement at a reduced size and
+    through size-independent properties at full size.
+Tolerances: integer disparities, the invalid mask and every float tap are compared BIT-EXACT (stricter
+than north_star's 1e-3 px for sub-pixel values).
+"""
+import numpy as np
+import pytest
+
+from oracle import refbind, restate
+from stereo_matching_b200 import capi, synth
+from tests.common import bits_equal, case_inputs, n_diff
+
+pytestmark = pytest.mark.gpu
+H = restate.fnv1a64
+
+
+def _check_sgm_against_restatement(L, R, scale, d, sl=None, sr=None, paths=8):
+    want = restate.process(L, R, scale, d, "sgm", sl, sr, taps=restate.ALL_TAPS, paths=paths)
+    sv = capi.SGM(L.shape[0], L.shape[1], scale, d, flags=capi.FLAG_KEEP_VOLUMES, paths=paths)
+    sv.process(L, R, sl, sr)
+    bad = {}
+    for v in (0, 1):
+        for tap, key in (("blur", "blur"), ("census", "census"), ("cost", "cost_hv"), ("pathsum", "S"), ("disp", "disp"),
+                         ("subpixel", "fsub")):
+            nd = n_diff(sv.tap(tap, v), want[key][v])
+            if nd:
+                bad[f"{tap}[{v}]"] = nd
+    for tap, key in (("lr", "f_lr"), ("median", "f_median"), ("final", "f_final")):
+        nd = n_diff(sv.tap(tap), want[key])
+        if nd:
+            bad[tap] = nd
+    nd = n_diff(sv.get_disp(), want["f_final"])
+    if nd:
+        bad["get_disp"] = nd
+    sv.close()
+    assert not bad, f"stages differing from the oracle (count of differing elements): {bad}"
+    return want
+
+
+@pytest.mark.parametrize("h,w,d,scale,noise,sky", [
+    (96, 160, 32, 1, 6, False),
+    (120, 200, 64, 1, 40, True),
+    (200, 320, 64, 2, 10, True),
+    (64, 300, 128, 1, 25, False),
+    (97, 161, 64, 1, 60, False),   # odd sizes, heavy noise: many holes for the median / speckle stages
+    (300, 200, 32, 1, 12, True),   # W < H
+])
+def test_sgm_stages_bit_exact_vs_oracle(h, w, d, scale, noise, sky):
+    L, R, _ = synth.random_dot_pair(h, w, seed=h * 7 + d, bg=5, fg=min(17, d // 2), noise=noise)
+    sl, sr = synth.sky_masks(h // scale, w // scale) if sky else (None, None)
+    want = _check_sgm_against_restatement(L, R, scale, d, sl, sr)
+    assert (want["f_final"] <= d - 1).any()
+
+
+def test_sgm_four_paths_vs_oracle():
+    L, R, _ = synth.random_dot_pair(80, 144, seed=21, bg=4, fg=13, noise=10)
+    _check_sgm_against_restatement(L, R, 1, 64, paths=4)
+
+
+def test_sgm_subpixel_slanted_plane():
+    L, R, gt = synth.slanted_pair(128, 256, d0=6.0, d1=40.0)
+    want = _check_sgm_against_restatement(L, R, 1, 64)
+    f = want["f_final"]
+    ok = (f <= 63) & (np.arange(256)[None, :] >= 64)
+    assert ok.sum() > 1000 and np.abs(f[ok] - gt[ok]).mean() < 1.0
+    assert (f[ok] != np.floor(f[ok])).mean() > 0.3  # the parabola fit really produces fractions
+
+
+def test_sgm_widened_d256_vs_restatement():
+    # D=256 cannot run through the reference (src/Solver.cpp:10); oracle = widened restatement
+    L, R, _ = synth.random_dot_pair(72, 480, seed=4, bg=24, fg=200, noise=6)
+    _check_sgm_against_restatement(L, R, 1, 256)
+
+
+@pytest.mark.skipif(not refbind.available(), reason="compiled reference (oracle/_ref) did not travel")
+def test_sgm_against_compiled_reference_live():
+    h, w, d = 150, 400, 64
+    L, R, _ = synth.random_dot_pair(h, w, seed=77, bg=9, fg=30, noise=20)
+    sl, sr = synth.sky_masks(h, w, 0.2)
+    refbind.set_threads(1)
+    ref = refbind.process("sgm", L, R, 1, d, sl, sr, want_cost=True)
+    sv = capi.SGM(h, w, 1, d, flags=capi.FLAG_KEEP_VOLUMES)
+    sv.process(L, R, sl, sr)
+    assert bits_equal(sv.get_disp_u8(0), ref["disp"])
+    assert bits_equal(sv.get_disp_u8(1), ref["disp_beta"])
+    assert bits_equal(sv.tap("pathsum", 1), ref["cost_last"])
+    assert bits_equal(sv.tap("subpixel", 1), ref["fdisp_beta"])
+    got, want = sv.get_disp(), ref["fdisp"]
+    assert np.array_equal(got > d - 1, want > d - 1)          # invalid mask exact
+    assert np.abs(got - want).max() <= 1e-3                      # north_star tolerance ...
+    assert bits_equal(got, want)                                 # ... and in fact bit-equal
+    for beta, m in ((False, sl), (True, sr)):
+        st = refbind.stages("sgm", L, R, 1, d, beta=beta, sky=m)
+        assert bits_equal(sv.tap("cost", int(beta)), st["cost_hv"])
+    assert bits_equal(sv.tap("census", 0), st["ct_l"]) and bits_equal(sv.tap("census", 1), st["ct_r"])
+    bm = capi.BM(h, w, 1, d)
+    bm.process(L, R, sl, sr)
+    assert bits_equal(bm.get_disp_u8(0), refbind.process("bm", L, R, 1, d, sl, sr)["disp"])
+
+
+KITTI_SGM = ["kitti_sgm_d128_clean", "kitti_sgm_d64_clean", "kitti_sgm_d128_noisy_sky", "kitti_sgm_d64_noisy",
+             "kitti_sgm_d64_scale2", "odd_sgm_d32", "tall_sgm_d32"]
+
+
+@pytest.mark.parametrize("name", KITTI_SGM)
+def test_sgm_kitti_size_against_reference_golden(golden, name):
+    c = golden[name]
+    L, R, (sl, sr) = case_inputs(c)
+    want = c["hashes"]
+    assert (H(L), H(R)) == (want["left"], want["right"])
+    sv = capi.SGM(c["h"], c["w"], c["scale"], c["d"], flags=capi.FLAG_KEEP_VOLUMES)
+    sv.process(L, R, sl, sr)
+    got = dict(census_l=H(sv.tap("census", 0)), census_r=H(sv.tap("census", 1)), cost_hv_l=H(sv.tap("cost", 0)),
+               cost_hv_r=H(sv.tap("cost", 1)), S_r=H(sv.tap("pathsum", 1)), disp=H(sv.get_disp_u8(0)),
+               disp_beta=H(sv.get_disp_u8(1)), fsub_r=H(sv.tap("subpixel", 1)), f_final=H(sv.get_disp()))
+    bad = {k: (v, want[k]) for k, v in got.items() if v != want[k]}
+    assert not bad, f"{name}: taps whose hash differs from the reference: {sorted(bad)}"
+    f = sv.get_disp()
+    assert int((f <= c["d"] - 1).sum()) == c["stats"]["valid"]
+    sv.close()
+
+
+@pytest.mark.parametrize("name", ["kitti_bm_d64_clean", "kitti_bm_d64_noisy"])
+def test_bm_kitti_size_against_reference_golden(golden, name):
+    c = golden[name]
+    L, R, _ = case_inputs(c)
+    bm = capi.BM(c["h"], c["w"], c["scale"], c["d"])
+    bm.process(L, R)
+    want = c["hashes"]
+    assert H(bm.tap("census", 0)) == want["census_l"] and H(bm.tap("cost", 0)) == want["cost_hv_l"]
+    assert H(bm.get_disp_u8(0)) == want["disp"]
+    bm.close()
+
+
+@pytest.mark.parametrize("h,w,d,scale,noise", [(96, 160, 32, 1, 10), (150, 260, 64, 2, 30), (80, 200, 128, 1, 50)])
+def test_bm_census_vs_oracle(h, w, d, scale, noise):
+    L, R, _ = synth.random_dot_pair(h, w, seed=h + d, bg=4, fg=12, noise=noise)
+    want = restate.process(L, R, scale, d, "bm", taps=restate.ALL_TAPS)
+    bm = capi.BM(h, w, scale, d)
+    bm.process(L, R)
+    assert bits_equal(bm.tap("cost", 0), want["cost_hv"][0])
+    assert n_diff(bm.tap("disp", 0), want["disp"][0]) == 0
+    assert bits_equal(bm.tap("subpixel", 0), want["fsub"][0])
+    assert bits_equal(bm.tap("median"), want["f_median"]) and bits_equal(bm.get_disp(), want["f_final"])
+    bm.close()
+
+
+@pytest.mark.parametrize("h,w,d,scale,noise", [(64, 128, 32, 1, 8), (90, 250, 64, 1, 30), (120, 200, 64, 2, 12)])
+def test_bm_sad_vs_oracle(h, w, d, scale, noise):
+    # BASELINE.json config 2 (SAD 9x9 + WTA + LR-check): oracle = restatement built on the reference's SAD()
+    L, R, _ = synth.random_dot_pair(h, w, seed=h * 3 + d, bg=4, fg=12, noise=noise)
+    want = restate.process(L, R, scale, d, "bm_sad", taps=restate.ALL_TAPS)
+    bm = capi.BMSad(h, w, scale, d)
+    bm.process(L, R)
+    for v in (0, 1):
+        assert bits_equal(bm.tap("cost", v), want["cost_raw"][v]), f"SAD volume view {v}"
+        assert n_diff(bm.tap("disp", v), want["disp"][v]) == 0
+    assert bits_equal(bm.tap("lr"), want["f_lr"])
+    assert bits_equal(bm.tap("median"), want["f_median"]) and bits_equal(bm.get_disp(), want["f_final"])
+    bm.close()
+
+
+def test_dense_sad_entry_point_vs_oracle():
+    L, R, _ = synth.random_dot_pair(40, 70, seed=2, bg=3, fg=7, noise=12)
+    for wh, ww in ((9, 9), (7, 9), (3, 5)):
+        want = restate.process(L, R, 1, 32, "bm_sad", taps=("cost_raw",), sad_h=wh, sad_w=ww)["cost_raw"][0]
+        assert bits_equal(capi.cost_volume_sad(L, R, 32, wh, ww), want), (wh, ww)
+
+
+def test_strided_inputs_repeat_and_two_handles():
+    h, w, d = 64, 160, 32
+    L, R, _ = synth.random_dot_pair(h, w, seed=9, bg=4, fg=11, noise=10)
+    want = restate.process(L, R, 1, d, "sgm")["f_final"]
+    big_l, big_r = np.zeros((h, w + 37), np.uint8), np.zeros((h, w + 5), np.uint8)
+    big_l[:, :w], big_r[:, :w] = L, R
+    a, b = capi.SGM(h, w, 1, d), capi.SGM(h, w, 1, d)
+    a.enqueue(big_l[:, :w], big_r[:, :w])
+    b.enqueue(L, R)
+    a.wait(), b.wait()
+    assert bits_equal(a.get_disp(), want) and bits_equal(b.get_disp(), want)
+    for _ in range(3):  # the handle is reusable and deterministic
+        a.process(L, R)
+        assert bits_equal(a.get_disp(), want)
+    assert a.launches > 0
+    a.close(), b.close()
+
+
+def test_device_resident_inputs_match_host_path():
+    torch = pytest.importorskip("torch")
+    h, w, d = 96, 192, 64
+    L, R, _ = synth.random_dot_pair(h, w, seed=10, bg=6, fg=20, noise=10)
+    sv = capi.SGM(h, w, 1, d)
+    want = sv.process(L, R).get_disp()
+    tl, tr = torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()
+    torch.cuda.synchronize()
+    sv.enqueue_device(tl.data_ptr(), w, tr.data_ptr(), w)
+    sv.wait()
+    assert bits_equal(sv.get_disp(), want)
+    sv.close()
+
+
+def test_error_codes_instead_of_asserts():
+    with pytest.raises(capi.SgmError) as e:
+        capi.SGM(100, 100, 3, 64)          # src/Solver.cpp:8 asserts scale in {1,2}
+    assert e.value.code == 1
+    with pytest.raises(capi.SgmError) as e:
+        capi.SGM(100, 100, 1, 48)          # src/Solver.cpp:10 asserts d in {32,64,128}
+    assert e.value.code == 2
+    with pytest.raises(capi.SgmError):
+        capi.SGM(0, 100, 1, 64)
+    sv = capi.SGM(64, 64, 1, 32)
+    with pytest.raises(capi.SgmError):
+        sv.get_disp()                       # nothing processed yet
+    with pytest.raises(capi.SgmError):
+        sv.process(np.zeros((64, 64), np.float32), np.zeros((64, 64), np.uint8))   # src/SGM.cpp:38
+    with pytest.raises(capi.SgmError):
+        sv.process(np.zeros((64, 65), np.uint8), np.zeros((64, 65), np.uint8))     # src/SGM.cpp:34-35
+    with pytest.raises(capi.SgmError):
+        sv.get_disp_u8(2)
+    sv.close()
+
+
+def test_full_size_1080p_d256_properties():
+    # BASELINE.json config 4: the reference cannot run it; check size-independent properties at full size
+    h, w, d = 1080, 1920, 256
+    L, R, gt = synth.random_dot_pair(h, w, seed=31, bg=24, fg=200)
+    sv = capi.SGM(h, w, 1, d)
+    f1 = sv.process(L, R).get_disp()
+    f2 = sv.process(L, R).get_disp()
+    assert bits_equal(f1, f2)                                   # deterministic
+    valid = f1 <= d - 1
+    cols = np.arange(w)[None, :] >= d
+    good = valid & cols & (np.abs(f1 - gt) <= 1)
+    assert good.sum() > 0.9 * cols.sum() * h / h and (valid & cols).mean() > 0.7
+    d16 = sv.get_disp_u16(0)
+    assert d16.max() <= d + 1 and set(np.unique(f1[~valid])) == {float(d + 1)}
+    # a frame that is constant along x has no texture: identical left/right => disparity 0 or invalid everywhere
+    flat = np.repeat(np.arange(h, dtype=np.uint8)[:, None] * 3, w, axis=1)
+    f3 = sv.process(flat, flat).get_disp()
+    assert set(np.unique(f3)) <= {0.0, float(d + 1)}
+    sv.close()
