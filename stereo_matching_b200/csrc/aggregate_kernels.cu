@@ -5,8 +5,9 @@
 //
 // Shape: one warp walks one scanline of one path direction; the D disparities of the current pixel
 // live in registers spread over the 32 lanes (LaneLayout), d+-1 neighbours come from two lane rotations
-// per chunk, the min over disparities is a single warp REDUX on the (non-negative) float bit patterns
-// and the 3-way min of the recurrence is a DPX VIMNMX3.  Diagonal lines wrap around the image sides and
+// per chunk, the min over disparities is a single Blackwell CREDUX.MIN.F32 (redux.sync.min.f32) and the 3-way
+// min of the recurrence is one FMNMX3 (costs can be negative under a sky mask, so the integer DPX forms
+// would not be exact; see common.cuh).  Diagonal lines wrap around the image sides and
 // re-initialise there exactly where the reference does (src/SGM.cpp:266,282,330,346), so every warp is
 // independent of every other one: no inter-block communication.
 //
@@ -77,7 +78,7 @@ __device__ __forceinline__ void path_step(float (&L)[LaneLayout<D>::E], const fl
             else
                 hi = lane < 31 ? dn[q] : (q < NCH - 1 ? dn[q < NCH - 1 ? q + 1 : q] : L[k]);
             const float nb = __fadd_rn(fminf(lo, hi), P1);
-            const float t = min3_nonneg(nb, L[k], mP2);
+            const float t = min3f(nb, L[k], mP2);
             nL[k] = __fadd_rn(t, __fsub_rn(C[k], m));
         }
     }
@@ -87,7 +88,7 @@ __device__ __forceinline__ void path_step(float (&L)[LaneLayout<D>::E], const fl
         L[k] = nL[k];
         lm = fminf(lm, nL[k]);
     }
-    m = warp_min_nonneg(lm);
+    m = warp_min_f32(lm);
 }
 
 // WTA + uniqueness + sub-pixel on one pixel's summed costs held across the warp.
@@ -100,45 +101,41 @@ __device__ __forceinline__ void wta_pixel(const float (&S)[LaneLayout<D>::E], in
     using LL = LaneLayout<D>;
     constexpr int E = LL::E;
     constexpr int NONE = 0x7fffffff;
-    int sb[E];
+    float lmin = S[0];
 #pragma unroll
-    for (int k = 0; k < E; ++k) sb[k] = __float_as_int(S[k]);
-    int lmin = sb[0];
-#pragma unroll
-    for (int k = 1; k < E; ++k) lmin = min(lmin, sb[k]);
-    const int gmin = __reduce_min_sync(FULL_MASK, lmin);
-    int lidx = NONE, lsec = NONE;
+    for (int k = 1; k < E; ++k) lmin = fminf(lmin, S[k]);
+    const float gmin = warp_min_f32(lmin);
+    int lidx = NONE;
+    float lsec = INFINITY;  // costs are finite, so +inf marks "no second distinct value" (sec_min_cost = FLT_MAX path)
 #pragma unroll
     for (int k = 0; k < E; ++k) {
-        if (sb[k] == gmin)
+        if (S[k] == gmin)
             lidx = min(lidx, LL::disparity(lane, k));
         else
-            lsec = min(lsec, sb[k]);
+            lsec = fminf(lsec, S[k]);
     }
     const int min_d = __reduce_min_sync(FULL_MASK, lidx);
-    const int gsec = __reduce_min_sync(FULL_MASK, lsec);
+    const float gsec = warp_min_f32(lsec);
     int lsidx = NONE;
 #pragma unroll
     for (int k = 0; k < E; ++k)
-        if (sb[k] == gsec) lsidx = min(lsidx, LL::disparity(lane, k));
+        if (S[k] == gsec) lsidx = min(lsidx, LL::disparity(lane, k));
     const int sec_d = __reduce_min_sync(FULL_MASK, lsidx);
     // neighbours of the winner for the parabola (0 bits where this lane does not own them)
     int bm = 0, bp = 0;
 #pragma unroll
     for (int k = 0; k < E; ++k) {
         const int dk = LL::disparity(lane, k);
-        if (dk == min_d - 1) bm = sb[k];
-        if (dk == min_d + 1) bp = sb[k];
+        if (dk == min_d - 1) bm = __float_as_int(S[k]);
+        if (dk == min_d + 1) bp = __float_as_int(S[k]);
     }
     bm = __reduce_or_sync(FULL_MASK, (unsigned)bm);
     bp = __reduce_or_sync(FULL_MASK, (unsigned)bp);
 
-    const float c0 = __int_as_float(gmin);
+    const float c0 = gmin;
     bool invalid = false;
-    if (gsec != NONE) {  // a second distinct value exists; otherwise sec_min_cost stays FLT_MAX and the ratio test fails
-        const float sec = __int_as_float(gsec);
-        invalid = (__fdiv_rn(c0, sec) > ratio) && (abs(min_d - sec_d) > min_gap);
-    }
+    if (gsec != INFINITY)  // a second distinct value exists; otherwise sec_min_cost stays FLT_MAX and the ratio test fails
+        invalid = (__fdiv_rn(c0, gsec) > ratio) && (abs(min_d - sec_d) > min_gap);
     if (invalid) {
         disp_out = D + 1;
         sub_out = (float)(D + 1);
@@ -230,7 +227,7 @@ __global__ void __launch_bounds__(WARPS_PER_BLOCK * 32) sgm_path_kernel(const Pa
                         L[k] = Cb[u][k];
                         lm = fminf(lm, L[k]);
                     }
-                    m = warp_min_nonneg(lm);
+                    m = warp_min_f32(lm);
                 } else {
                     path_step<D>(L, Cb[u], m, lane, a.P1, a.P2);
                 }
@@ -298,7 +295,7 @@ void launch_path(const PathArgs& pa, int views, cudaStream_t st, LaunchCounter& 
     const int nlines = pa.di == 0 ? pa.h : pa.w;
     dim3 grid((nlines + WARPS_PER_BLOCK - 1) / WARPS_PER_BLOCK, views);
     sgm_path_kernel<D, MODE, PF><<<grid, WARPS_PER_BLOCK * 32, 0, st>>>(pa);
-    lc.note();
+    lc.note("sgm_path_kernel");
 }
 
 template <int D>
@@ -369,7 +366,7 @@ void launch_wta(const float* vol, uint16_t* disp, float* subpixel, int views, in
         case 256: wta_volume_kernel<256><<<blocks, 256, 0, st>>>(vol, disp, subpixel, npix, unique_ratio, min_gap, parabola); break;
         default: lc.err = cudaErrorInvalidValue; return;
     }
-    lc.note();
+    lc.note("wta_volume_kernel");
 }
 
 }  // namespace sgmb200

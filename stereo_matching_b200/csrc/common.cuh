@@ -81,14 +81,16 @@ __device__ __forceinline__ void store_pixel(float* pix, int lane, const float (&
     for (int q = 0; q < LL::NCH; ++q) VecIO<LL::CW>::store(pix + q * LL::CHUNK_SPAN + lane * LL::CW, &v[q * LL::CW]);
 }
 
-// All costs on the path are non-negative, finite floats (L >= 0 is shown in DESIGN.md),
-// so float order == signed-integer order of the bit patterns.  That lets the 3-way min of the SGM
-// recurrence run on the DPX pipe (VIMNMX3) and the min over disparities be one warp REDUX.
-__device__ __forceinline__ float min3_nonneg(float a, float b, float c) {
-    return __int_as_float(__vimin3_s32(__float_as_int(a), __float_as_int(b), __float_as_int(c)));
-}
-__device__ __forceinline__ float warp_min_nonneg(float v) {
-    return __int_as_float(__reduce_min_sync(FULL_MASK, __float_as_int(v)));
+// Costs on the path are finite floats but NOT sign-definite: with a sky mask the in-place recursive box
+// filter cancels 999999-sized terms and leaves negative costs below the sky boundary (measured: down to -3.7e4),
+// so integer (DPX VIMNMX) tricks on the bit patterns would be wrong.  Blackwell has the float forms natively:
+// FMNMX3 (3-input float min, what fminf(fminf(a, b), c) compiles to on sm_100a) and CREDUX.MIN.F32
+// (redux.sync.min.f32, one instruction for the min over the 32 lanes).
+__device__ __forceinline__ float min3f(float a, float b, float c) { return fminf(fminf(a, b), c); }
+__device__ __forceinline__ float warp_min_f32(float v) {
+    float r;
+    asm volatile("redux.sync.min.f32 %0, %1, 0xffffffff;" : "=f"(r) : "f"(v));
+    return r;
 }
 
 }  // namespace sgmb200

@@ -243,13 +243,13 @@ void launch_subsample(const uint8_t* src, size_t src_stride, int col_step, int r
                       cudaStream_t st, LaunchCounter& lc) {
     dim3 grid((iw + 255) / 256, ih);
     subsample_kernel<<<grid, 256, 0, st>>>(src, src_stride, col_step, row_step, dst, ih, iw);
-    lc.note();
+    lc.note("subsample_kernel");
 }
 
 void launch_blur3(const uint8_t* src, uint8_t* dst, int h, int w, cudaStream_t st, LaunchCounter& lc) {
     dim3 grid((w + 255) / 256, h, 2);
     blur3_kernel<<<grid, 256, 0, st>>>(src, dst, h, w);
-    lc.note();
+    lc.note("blur3_kernel");
 }
 
 void launch_census(const uint8_t* img, uint64_t* table, int h, int w, int win_h, int win_w, cudaStream_t st,
@@ -261,7 +261,7 @@ void launch_census(const uint8_t* img, uint64_t* table, int h, int w, int win_h,
     }
     dim3 grid((w + CT_TX - 1) / CT_TX, (h + CT_TY - 1) / CT_TY, 2);
     census_kernel<<<grid, dim3(CT_TX, CT_TY), 0, st>>>(img, table, h, w, rh, rw);
-    lc.note();
+    lc.note("census_kernel");
 }
 
 void launch_hamming_hfilter(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r,
@@ -276,7 +276,7 @@ void launch_hamming_hfilter(const uint64_t* ct_l, const uint64_t* ct_r, const ui
         case 1: hamming_hfilter_kernel<1><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale); break;
         default: lc.err = cudaErrorInvalidValue; return;
     }
-    lc.note();
+    lc.note("hamming_hfilter_kernel");
 }
 
 void launch_vfilter(float* cost, int views, int h, int w, int d, int win, cudaStream_t st, LaunchCounter& lc) {
@@ -289,7 +289,7 @@ void launch_vfilter(float* cost, int views, int h, int w, int d, int win, cudaSt
         case 1: vfilter_kernel<1><<<grid, 256, 0, st>>>(cost, h, w, d); break;
         default: lc.err = cudaErrorInvalidValue; return;
     }
-    lc.note();
+    lc.note("vfilter_kernel");
 }
 
 void launch_sad_volume(const uint8_t* img_l, const uint8_t* img_r, float* cost, int views, int h, int w, int d, int win_h,
@@ -302,7 +302,7 @@ void launch_sad_volume(const uint8_t* img_l, const uint8_t* img_r, float* cost, 
     }
     dim3 grid((w + SAD_TJ - 1) / SAD_TJ, h, views);
     sad_volume_kernel<<<grid, 256, smem, st>>>(img_l, img_r, cost, h, w, d, win_h, win_w, scale);
-    lc.note();
+    lc.note("sad_volume_kernel");
 }
 
 }  // namespace sgmb200

@@ -298,7 +298,8 @@ int run_frame(sgm_engine* e, const uint8_t* left, size_t lstride, const uint8_t*
     launch_speckle(e->d_med, e->d_final, e->d_label, e->d_area, h, w, (float)(D + 1), p.speckle_size / s, (float)p.speckle_dis, st,
                    lc);                                                              // src/Solver.cpp:634
     if (e->timing) cudaEventRecord(e->ev[SGM_STAGE_DOWNLOAD], st);
-    if (lc.err != cudaSuccess) return fail(e, SGM_ERR_CUDA, "kernel launch failed: %s", cudaGetErrorString(lc.err));
+    if (lc.err != cudaSuccess)
+        return fail(e, SGM_ERR_CUDA, "%s failed: %s", lc.failed ? lc.failed : "kernel launch", cudaGetErrorString(lc.err));
     return SGM_OK;
 }
 
@@ -342,6 +343,8 @@ int sgm_enqueue(sgm_engine* e, const uint8_t* left, size_t ls, const uint8_t* ri
     if (sky_l) CU_TRY(e, cudaMemcpyAsync(e->d_sky[0], e->h_sky[0], e->n, cudaMemcpyHostToDevice, st));
     if (sky_r) CU_TRY(e, cudaMemcpyAsync(e->d_sky[1], e->h_sky[1], e->n, cudaMemcpyHostToDevice, st));
     LaunchCounter lc;
+    lc.stream = st;
+    lc.sync_each = std::getenv("SGM_B200_DEBUG_SYNC") != nullptr;
     rc = run_frame(e, e->d_in[0], W, e->d_in[1], W, sky_l ? e->d_sky[0] : nullptr, sky_r ? e->d_sky[1] : nullptr, lc);
     e->launches = lc.launches;
     if (rc != SGM_OK) return rc;
@@ -370,6 +373,8 @@ int sgm_enqueue_device(sgm_engine* e, const void* left, size_t ls, const void* r
         sr = e->d_sky[1];
     }
     LaunchCounter lc;
+    lc.stream = st;
+    lc.sync_each = std::getenv("SGM_B200_DEBUG_SYNC") != nullptr;
     rc = run_frame(e, static_cast<const uint8_t*>(left), ls, static_cast<const uint8_t*>(right), rs, sl, sr, lc);
     e->launches = lc.launches;
     if (rc != SGM_OK) return rc;

@@ -12,10 +12,17 @@ namespace sgmb200 {
 struct LaunchCounter {
     int launches = 0;
     cudaError_t err = cudaSuccess;
-    void note() {
+    const char* failed = nullptr;   // name of the first launch that failed
+    bool sync_each = false;         // SGM_B200_DEBUG_SYNC=1: synchronise after every launch to localise a fault
+    cudaStream_t stream = nullptr;
+    void note(const char* name = "kernel") {
         ++launches;
         cudaError_t e = cudaGetLastError();
-        if (err == cudaSuccess && e != cudaSuccess) err = e;
+        if (e == cudaSuccess && sync_each) e = cudaStreamSynchronize(stream);
+        if (err == cudaSuccess && e != cudaSuccess) {
+            err = e;
+            failed = name;
+        }
     }
 };
 

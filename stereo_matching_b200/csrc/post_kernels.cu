@@ -20,8 +20,12 @@ __global__ void lr_check_kernel(const float* __restrict__ left, const float* __r
     float dl = left[p];
     if ((float)j >= dl) {
         const int jr = (int)__fsub_rn((float)j, __fdiv_rn(dl, (float)scale));
-        const float dr = right[(size_t)i * w + jr];
-        if (fabsf(__fsub_rn(dl, dr)) > thresh) dl = (float)(d + 1);
+        // 0 <= jr <= j holds for every finite dl >= 0; the guard only keeps a non-finite dl (which the reference
+        // would index out of bounds with) from faulting
+        if (jr >= 0 && jr < w) {
+            const float dr = right[(size_t)i * w + jr];
+            if (fabsf(__fsub_rn(dl, dr)) > thresh) dl = (float)(d + 1);
+        }
     }
     out_keep[p] = dl;
     out_work[p] = dl;
@@ -169,7 +173,7 @@ void launch_lr_check(const float* left, const float* right, float* out_keep, flo
                      float thresh, cudaStream_t st, LaunchCounter& lc) {
     dim3 grid((w + 255) / 256, h);
     lr_check_kernel<<<grid, 256, 0, st>>>(left, right, out_keep, out_work, h, w, d, scale, thresh);
-    lc.note();
+    lc.note("lr_check_kernel");
 }
 
 void launch_median_fill(const float* src, float* f, int h, int w, int d, int win_h, int win_w, cudaStream_t st,
@@ -184,21 +188,21 @@ void launch_median_fill(const float* src, float* f, int h, int w, int d, int win
         lc.err = cudaErrorInvalidValue;
         return;
     }
-    lc.note();
+    lc.note("median_fill_kernel");
 }
 
 void launch_speckle(const float* f, float* f_out, int* labels, int* area, int h, int w, float value, int max_size,
                     float max_dis, cudaStream_t st, LaunchCounter& lc) {
     const int n = h * w;
     speckle_rows_kernel<<<(h + 7) / 8, 256, 0, st>>>(f, labels, area, h, w, max_dis);
-    lc.note();
+    lc.note("speckle_rows_kernel");
     dim3 grid((w + 255) / 256, h);
     speckle_merge_kernel<<<grid, 256, 0, st>>>(f, labels, h, w, max_dis);
-    lc.note();
+    lc.note("speckle_merge_kernel");
     speckle_count_kernel<<<(n + 255) / 256, 256, 0, st>>>(labels, area, n);
-    lc.note();
+    lc.note("speckle_count_kernel");
     speckle_apply_kernel<<<(n + 255) / 256, 256, 0, st>>>(f, f_out, labels, area, n, value, max_size);
-    lc.note();
+    lc.note("speckle_apply_kernel");
 }
 
 }  // namespace sgmb200

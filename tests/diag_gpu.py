@@ -60,15 +60,18 @@ def run(h, w, d, scale, noise=12, sky=False, algo="sgm", paths=8):
 
 
 if __name__ == "__main__":
-    if len(sys.argv) >= 5:
-        run(*map(int, sys.argv[1:5]))
+    if len(sys.argv) >= 2:
+        a = sys.argv[1:]
+        run(int(a[0]), int(a[1]), int(a[2]), int(a[3]), noise=int(a[4]), sky=bool(int(a[5])), algo=a[6], paths=int(a[7]))
     else:
-        run(96, 160, 32, 1)
-        run(120, 200, 64, 1, noise=40, sky=True)
-        run(64, 300, 128, 1, noise=25)
-        run(200, 320, 64, 2, noise=10, sky=True)
-        run(72, 480, 256, 1, noise=6)
-        run(80, 144, 64, 1, paths=4)
-        run(96, 160, 32, 1, algo="bm")
-        run(90, 250, 64, 1, noise=30, algo="bm_sad")
-        run(375, 1242, 128, 1, noise=8)
+        import subprocess
+
+        cases = ["96 160 32 1 12 0 sgm 8", "120 200 64 1 12 0 sgm 8", "120 200 64 1 40 0 sgm 8", "120 200 64 1 12 1 sgm 8",
+                 "64 300 128 1 25 0 sgm 8", "200 320 64 2 10 1 sgm 8", "72 480 256 1 6 0 sgm 8", "80 144 64 1 12 0 sgm 4",
+                 "96 160 32 1 12 0 bm 8", "90 250 64 1 30 0 bm_sad 8", "375 1242 128 1 8 0 sgm 8"]
+        for c in cases:
+            r = subprocess.run([sys.executable, __file__] + c.split(), capture_output=True, text=True)
+            print(r.stdout, end="")
+            if r.returncode != 0:
+                print(f"== CASE {c} FAILED rc={r.returncode}: {r.stderr.strip().splitlines()[-1] if r.stderr.strip() else ''}")
+            sys.stdout.flush()
