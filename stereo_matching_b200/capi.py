@@ -170,6 +170,10 @@ class Solver:
         self._check(lib().sgm_get_disparity_f32(self._h, out.ctypes.data, out.strides[0]))
         return out
 
+    def get_disp_into(self, out: np.ndarray) -> None:
+        """get_disp() into a caller-owned float32 (img_h, img_w) array (no allocation)."""
+        self._check(lib().sgm_get_disparity_f32(self._h, out.ctypes.data, out.strides[0]))
+
     def get_disp_u8(self, view=0) -> np.ndarray:
         out = np.empty((self.img_h, self.img_w), np.uint8)
         self._check(lib().sgm_get_disparity_u8(self._h, view, out.ctypes.data, out.strides[0]))
@@ -199,6 +203,11 @@ class Solver:
         ms = (C.c_float * len(STAGES))()
         self._check(lib().sgm_get_stage_ms(self._h, ms, len(STAGES)))
         return dict(zip(STAGES, list(ms)))
+
+    @property
+    def stream_ptr(self) -> int:
+        """cudaStream_t the engine launches on (for CUDA-event timing on the launching stream)."""
+        return lib().sgm_get_stream(self._h)
 
     def disparity_device_ptr(self) -> int:
         return lib().sgm_disparity_device(self._h)
