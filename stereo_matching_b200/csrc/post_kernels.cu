@@ -76,6 +76,85 @@ __global__ void __launch_bounds__(1024) median_fill_kernel(const float* __restri
     }
 }
 
+// Fast form of the same wavefront.  Every row keeps a 32-column ring in shared memory that holds the CURRENT
+// value of its pixels around the wavefront (final values behind the row's cursor, original values ahead of it);
+// with the skew K = RW+1 the window of any hole lies within +-(K*RH + RW) <= 8 columns of each neighbouring row's
+// cursor, so holes gather their 25 values from shared memory instead of L2.  Original values stream into the ring
+// with cp.async (LDGSTS, global -> shared without registers) issued LEAD steps before they are needed, one commit
+// group per step, so a step costs one barrier and a handful of instructions; the median of a filled hole is found
+// by bisection on the value (ints in [0, D-1]).
+template <int WH, int WW, int RPT>
+__global__ void __launch_bounds__(1024) median_fill_ring_kernel(const float* __restrict__ src, float* __restrict__ f, int h, int w,
+                                                                int d) {
+    constexpr int RH = WH / 2, RW = WW / 2, K = RW + 1, NWIN = WH * WW, RING = 32, AHEAD = K * RH + RW + 1, LEAD = 8;
+    static_assert(K * RH + RW <= 8 && AHEAD + LEAD + K * RH + RW < RING, "window does not fit the ring");
+    extern __shared__ float ring[];  // [h][RING]
+    const float vmax = (float)(d - 1);
+    const int T = blockDim.x;
+    // Row i's cursor at step t is column c = t - K*i.  At step t it requests the original of column c + AHEAD + LEAD;
+    // the request of step t-LEAD (column c + AHEAD) has landed before this step's barrier.
+    const int t_end = (w - 1) + K * (h - 1);
+    for (int t = -(AHEAD + LEAD); t <= t_end; ++t) {
+#pragma unroll
+        for (int rr = 0; rr < RPT; ++rr) {
+            const int i = threadIdx.x + rr * T;
+            if (i < h) {
+                const int cf = t - K * i + AHEAD + LEAD;
+                if (cf >= 0 && cf < w) {
+                    const unsigned dst = (unsigned)__cvta_generic_to_shared(ring + (size_t)i * RING + (cf & (RING - 1)));
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src + (size_t)i * w + cf));
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;");
+        asm volatile("cp.async.wait_group %0;" ::"n"(LEAD - 1));
+            __syncthreads();  // ring contents of this step's feeds and of the previous step's fills are visible
+#pragma unroll
+            for (int rr = 0; rr < RPT; ++rr) {
+                const int i = threadIdx.x + rr * T;
+                if (i >= RH && i < h - RH) {
+                    const int c = t - K * i;
+                    if (c >= RW && c < w - RW) {
+                        const float own = ring[(size_t)i * RING + (c & (RING - 1))];
+                        if (!(own <= vmax)) {  // a hole
+                            int vals[NWIN];
+                            int cnt = 0;
+#pragma unroll
+                            for (int a = -RH; a <= RH; ++a)
+#pragma unroll
+                                for (int b = -RW; b <= RW; ++b) {
+                                    const float v = ring[(size_t)(i + a) * RING + ((c + b) & (RING - 1))];
+                                    const bool ok = v <= vmax;
+                                    vals[(a + RH) * WW + (b + RW)] = ok ? (int)v : 0x7fffffff;  // float -> int truncation (:619)
+                                    cnt += ok ? 1 : 0;
+                                }
+                            if (cnt > NWIN / 2) {
+                                // sorted[cnt / 2] = smallest v with #(vals <= v) >= cnt/2 + 1; bisection over [0, D-1]
+                                const int need = cnt / 2 + 1;
+                                int lo = 0, hi = d - 1;
+                                while (lo < hi) {
+                                    const int mid = (lo + hi) >> 1;
+                                    int le = 0;
+#pragma unroll
+                                    for (int x = 0; x < NWIN; ++x) le += vals[x] <= mid ? 1 : 0;
+                                    if (le >= need)
+                                        hi = mid;
+                                    else
+                                        lo = mid + 1;
+                                }
+                                const float fill = (float)lo;
+                                f[(size_t)i * w + c] = fill;
+                                // publish for later pixels: nobody reads this ring slot before the next barrier
+                                ring[(size_t)i * RING + (c & (RING - 1))] = fill;
+                            }
+                        }
+                    }
+                }
+            }
+        // the fills written above are ordered before the next step's gathers by the next step's barrier
+    }
+}
+
 // ---- speckle filter: exact 4-connected components under |a - b| < max_dis (src/Solver.cpp:514-566) -----
 // Union-find with min-index roots.  Labels only ever decrease and always stay inside the component, so a
 // stale read merely costs extra hops.
@@ -180,7 +259,17 @@ void launch_median_fill(const float* src, float* f, int h, int w, int d, int win
                         LaunchCounter& lc) {
     int threads = ((h + 31) / 32) * 32;
     if (threads > 1024) threads = 1024;
-    if (win_h == 5 && win_w == 5)
+    const size_t ring_bytes = (size_t)h * 32 * sizeof(float);
+    if (win_h == 5 && win_w == 5 && ring_bytes <= 200 * 1024 && h <= 2048 && d <= 65536) {
+        // shared-memory ring form (the common case); the L2 form below stays as the fallback for very tall images
+        if (h <= 1024) {
+            cudaFuncSetAttribute(median_fill_ring_kernel<5, 5, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes);
+            median_fill_ring_kernel<5, 5, 1><<<1, threads, ring_bytes, st>>>(src, f, h, w, d);
+        } else {
+            cudaFuncSetAttribute(median_fill_ring_kernel<5, 5, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes);
+            median_fill_ring_kernel<5, 5, 2><<<1, 1024, ring_bytes, st>>>(src, f, h, w, d);
+        }
+    } else if (win_h == 5 && win_w == 5)
         median_fill_kernel<5, 5><<<1, threads, 0, st>>>(src, f, h, w, d);
     else if (win_h == 3 && win_w == 3)
         median_fill_kernel<3, 3><<<1, threads, 0, st>>>(src, f, h, w, d);
