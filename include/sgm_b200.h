@@ -70,6 +70,7 @@ typedef struct sgm_params {
 } sgm_params;
 
 #define SGM_FLAG_KEEP_VOLUMES 0x1u /* keep the summed path volume S of both views readable through sgm_get_tap (debug; costs 4 B per disp.px) */
+#define SGM_FLAG_LINE_WALKERS 0x4u /* aggregate with the independent line-walker kernels (8 launches, 88 B/disp.px) instead of the fused sweeps */
 #define SGM_FLAG_STAGE_TIMING 0x2u /* record CUDA events around the pipeline stages on the engine's stream (sgm_get_stage_ms) */
 
 /* Buffers readable after a frame, for parity tests and debugging (the reference keeps the same data in

@@ -45,6 +45,11 @@ struct sgm_engine {
     float* d_final = nullptr;                // [n]
     int* d_label = nullptr;                  // [n]
     int* d_area = nullptr;                   // [n]
+    float* d_halo = nullptr;                 // fused aggregation: cross-block halo ring
+    int* d_progress = nullptr;               // fused aggregation: per-block row counters
+    int* d_error = nullptr;                  // fused aggregation: time-out flag
+    int* h_error = nullptr;                  // pinned copy of d_error
+    bool fused = false;                      // last frame used the fused schedule
     // pinned host
     uint8_t* h_in[2] = {nullptr, nullptr};
     uint8_t* h_sky[2] = {nullptr, nullptr};
@@ -105,6 +110,10 @@ void release(sgm_engine* e) {
     cudaFree(e->d_final);
     cudaFree(e->d_label);
     cudaFree(e->d_area);
+    cudaFree(e->d_halo);
+    cudaFree(e->d_progress);
+    cudaFree(e->d_error);
+    cudaFreeHost(e->h_error);
     cudaFreeHost(e->h_final);
     for (auto& ev : e->ev)
         if (ev) cudaEventDestroy(ev);
@@ -209,7 +218,13 @@ int sgm_create(sgm_engine** out, const sgm_params* params) {
     ok = ok && dev_alloc(e, &e->d_cost, e->views * e->N) == cudaSuccess;
     if (p.algo == SGM_ALGO_SGM) {
         ok = ok && dev_alloc(e, &e->d_acc_a, e->views * e->N) == cudaSuccess;
-        if (p.paths == 8) ok = ok && dev_alloc(e, &e->d_acc_b, e->views * e->N) == cudaSuccess;
+        ok = ok && dev_alloc(e, &e->d_acc_b, e->views * e->N) == cudaSuccess;
+        ok = ok && dev_alloc(e, &e->d_halo, fused_halo_floats(e->views, iw, e->D)) == cudaSuccess;
+        ok = ok && dev_alloc(e, &e->d_progress, fused_progress_ints(e->views, iw)) == cudaSuccess;
+        ok = ok && dev_alloc(e, &e->d_error, 1) == cudaSuccess;
+        ok = ok && cudaMemset(e->d_error, 0, sizeof(int)) == cudaSuccess;
+        ok = ok && cudaMallocHost(reinterpret_cast<void**>(&e->h_error), sizeof(int)) == cudaSuccess;
+        if (ok) *e->h_error = 0;
         if (p.flags & SGM_FLAG_KEEP_VOLUMES) ok = ok && dev_alloc(e, &e->d_pathsum, e->views * e->N) == cudaSuccess;
     }
     ok = ok && dev_alloc(e, &e->d_disp, 2 * e->n) == cudaSuccess;
@@ -280,7 +295,14 @@ int run_frame(sgm_engine* e, const uint8_t* left, size_t lstride, const uint8_t*
         a.P2 = (float)p.P2;
         a.unique_ratio = p.unique_ratio;
         a.min_gap = 1;
-        launch_aggregate(a, st, lc);
+        a.halo = e->d_halo;
+        a.progress = e->d_progress;
+        a.error = e->d_error;
+        // fused three-launch schedule (sweep_kernels.cu) unless disabled or the image is too wide for a resident sweep
+        const bool want_fused = !(p.flags & SGM_FLAG_LINE_WALKERS) && std::getenv("SGM_B200_LINE_WALKERS") == nullptr;
+        e->fused = want_fused && launch_aggregate_fused(a, st, lc);
+        if (!e->fused) launch_aggregate(a, st, lc);
+        if (e->fused) cudaMemcpyAsync(e->h_error, e->d_error, sizeof(int), cudaMemcpyDeviceToHost, st);
     } else {
         // src/BM.cpp:52-91; census-BM gets compute_subpixel on the filtered cost, SAD-BM keeps integers
         launch_wta(e->d_cost, e->d_disp, e->d_sub, e->views, h, w, D, p.unique_ratio, 2, p.algo == SGM_ALGO_BM ? 1 : 0, st, lc);
@@ -391,6 +413,11 @@ int sgm_wait(sgm_engine* e) {
     cudaError_t c = cudaStreamSynchronize(e->stream);
     e->busy = false;
     if (c != cudaSuccess) return fail(e, SGM_ERR_CUDA, "frame failed: %s", cudaGetErrorString(c));
+    if (e->h_error && *e->h_error) {
+        *e->h_error = 0;
+        cudaMemset(e->d_error, 0, sizeof(int));
+        return fail(e, SGM_ERR_CUDA, "fused aggregation: a cross-block wait timed out (blocks not co-resident?)");
+    }
     e->have_result = true;
     if (e->timing) {
         for (int k = 0; k < SGM_STAGE_COUNT; ++k) {

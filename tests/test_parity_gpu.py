@@ -21,9 +21,9 @@ pytestmark = pytest.mark.gpu
 H = restate.fnv1a64
 
 
-def _check_sgm_against_restatement(L, R, scale, d, sl=None, sr=None, paths=8):
+def _check_sgm_against_restatement(L, R, scale, d, sl=None, sr=None, paths=8, flags=0):
     want = restate.process(L, R, scale, d, "sgm", sl, sr, taps=restate.ALL_TAPS, paths=paths)
-    sv = capi.SGM(L.shape[0], L.shape[1], scale, d, flags=capi.FLAG_KEEP_VOLUMES, paths=paths)
+    sv = capi.SGM(L.shape[0], L.shape[1], scale, d, flags=capi.FLAG_KEEP_VOLUMES | flags, paths=paths)
     sv.process(L, R, sl, sr)
     bad = {}
     for v in (0, 1):
@@ -59,9 +59,19 @@ def test_sgm_stages_bit_exact_vs_oracle(h, w, d, scale, noise, sky):
     assert (want["f_final"] <= d - 1).any()
 
 
-def test_sgm_four_paths_vs_oracle():
+@pytest.mark.parametrize("flags", [0, capi.FLAG_LINE_WALKERS])
+def test_sgm_four_paths_vs_oracle(flags):
     L, R, _ = synth.random_dot_pair(80, 144, seed=21, bg=4, fg=13, noise=10)
-    _check_sgm_against_restatement(L, R, 1, 64, paths=4)
+    _check_sgm_against_restatement(L, R, 1, 64, paths=4, flags=flags)
+
+
+@pytest.mark.parametrize("h,w,d,scale,sky", [(120, 200, 64, 1, True), (64, 300, 128, 1, False), (72, 250, 256, 1, False)])
+def test_sgm_line_walker_schedule_vs_oracle(h, w, d, scale, sky):
+    # the fall-back aggregation schedule (independent line walkers, used when an image is too wide for the resident
+    # fused sweeps) must give the same bits as the default fused schedule
+    L, R, _ = synth.random_dot_pair(h, w, seed=h + d, bg=5, fg=min(17, d // 2), noise=20)
+    sl, sr = synth.sky_masks(h // scale, w // scale) if sky else (None, None)
+    _check_sgm_against_restatement(L, R, scale, d, sl, sr, flags=capi.FLAG_LINE_WALKERS)
 
 
 def test_sgm_subpixel_slanted_plane():
