@@ -45,8 +45,8 @@ struct sgm_engine {
     float* d_final = nullptr;                // [n]
     int* d_label = nullptr;                  // [n]
     int* d_area = nullptr;                   // [n]
-    float* d_halo = nullptr;                 // fused aggregation: cross-block halo ring
-    int* d_progress = nullptr;               // fused aggregation: per-block row counters
+    float* d_halo = nullptr;                 // fused aggregation: cross-block halo ring (tagged payload)
+    unsigned halo_seq = 0;                   // fused aggregation: sweep launches so far (tag source)
     int* d_error = nullptr;                  // fused aggregation: time-out flag
     int* h_error = nullptr;                  // pinned copy of d_error
     bool fused = false;                      // last frame used the fused schedule
@@ -111,7 +111,6 @@ void release(sgm_engine* e) {
     cudaFree(e->d_label);
     cudaFree(e->d_area);
     cudaFree(e->d_halo);
-    cudaFree(e->d_progress);
     cudaFree(e->d_error);
     cudaFreeHost(e->h_error);
     cudaFreeHost(e->h_final);
@@ -219,8 +218,9 @@ int sgm_create(sgm_engine** out, const sgm_params* params) {
     if (p.algo == SGM_ALGO_SGM) {
         ok = ok && dev_alloc(e, &e->d_acc_a, e->views * e->N) == cudaSuccess;
         ok = ok && dev_alloc(e, &e->d_acc_b, e->views * e->N) == cudaSuccess;
-        ok = ok && dev_alloc(e, &e->d_halo, fused_halo_floats(e->views, iw, e->D)) == cudaSuccess;
-        ok = ok && dev_alloc(e, &e->d_progress, fused_progress_ints(e->views, iw)) == cudaSuccess;
+        const size_t halo_bytes = fused_halo_bytes(e->views, iw, e->D);
+        ok = ok && dev_alloc(e, &e->d_halo, halo_bytes / sizeof(float)) == cudaSuccess;
+        ok = ok && cudaMemset(e->d_halo, 0, halo_bytes) == cudaSuccess;
         ok = ok && dev_alloc(e, &e->d_error, 1) == cudaSuccess;
         ok = ok && cudaMemset(e->d_error, 0, sizeof(int)) == cudaSuccess;
         ok = ok && cudaMallocHost(reinterpret_cast<void**>(&e->h_error), sizeof(int)) == cudaSuccess;
@@ -296,7 +296,7 @@ int run_frame(sgm_engine* e, const uint8_t* left, size_t lstride, const uint8_t*
         a.unique_ratio = p.unique_ratio;
         a.min_gap = 1;
         a.halo = e->d_halo;
-        a.progress = e->d_progress;
+        a.launch_seq = &e->halo_seq;
         a.error = e->d_error;
         // fused three-launch schedule (sweep_kernels.cu) unless disabled or the image is too wide for a resident sweep
         const bool want_fused = !(p.flags & SGM_FLAG_LINE_WALKERS) && std::getenv("SGM_B200_LINE_WALKERS") == nullptr;

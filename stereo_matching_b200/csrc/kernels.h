@@ -59,9 +59,9 @@ struct AggregateArgs {
     float P1, P2, unique_ratio;
     int min_gap;        // 1 for SGM (src/SGM.cpp:409), 2 for BM (src/BM.cpp:82)
     // scratch of the fused schedule (sweep_kernels.cu); nullptr -> line walkers only
-    float* halo = nullptr;     // fused_halo_floats() floats
-    int* progress = nullptr;   // fused_progress_ints() ints
-    int* error = nullptr;      // 1 int, set when a cross-block wait timed out
+    float* halo = nullptr;          // fused_halo_bytes() bytes, zeroed once at allocation
+    unsigned* launch_seq = nullptr; // HOST counter of sweep launches that used `halo` (tags of the halo payload)
+    int* error = nullptr;           // 1 int, set when a cross-block wait timed out
 };
 // src/SGM.cpp:82-418 + compute_subpixel (src/Solver.cpp:569-597): the path recurrences, their sum in the
 // reference's association order, WTA, uniqueness and the sub-pixel parabola.
@@ -69,8 +69,7 @@ void launch_aggregate(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc
 // The same result with the fused three-launch schedule of sweep_kernels.cu (48 B instead of 88 B per disparity-pixel
 // and view).  Returns false without launching anything when the image is too wide for a resident sweep.
 bool launch_aggregate_fused(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc);
-size_t fused_halo_floats(int views, int w, int d);
-size_t fused_progress_ints(int views, int w);
+size_t fused_halo_bytes(int views, int w, int d);
 // src/BM.cpp:52-91 (+ compute_subpixel when parabola != 0): WTA / uniqueness straight on a cost volume.
 void launch_wta(const float* vol, uint16_t* disp, float* subpixel, int views, int h, int w, int d, float unique_ratio,
                 int min_gap, int parabola, cudaStream_t st, LaunchCounter& lc);

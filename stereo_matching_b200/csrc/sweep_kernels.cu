@@ -15,9 +15,10 @@
 //
 // Column neighbours inside a block exchange through shared memory (one barrier per row); the first / last
 // column of a block exchange with the neighbouring block through a small L2-resident halo ring in global memory
-// guarded by per-block progress counters (release / acquire).  A block only ever waits for its two neighbours'
-// PREVIOUS row, so all blocks advance within one row of their neighbours; the kernel is launched cooperatively so
-// that every block is resident, and every spin has a time-out that raises an error flag instead of hanging.
+// whose payload carries its own row tag (HaloIO below: no flags, no fences).  A block only ever waits for its two
+// neighbours' PREVIOUS row, so all blocks advance within one row of their neighbours; the kernel is launched
+// cooperatively so that every block is resident, and every wait has a time-out that raises an error flag instead of
+// hanging.
 #include "common.cuh"
 #include "kernels.h"
 #include "sgm_device.cuh"
@@ -26,8 +27,7 @@ namespace sgmb200 {
 
 namespace {
 
-constexpr int HALO_RING = 4;                       // rows of halo kept per block edge (2 would suffice)
-constexpr long long SPIN_TIMEOUT_CYCLES = 4000000000LL;  // ~2 s at 2 GHz
+constexpr int HALO_RING = 8;  // rows of halo kept per block edge (>= 4 is required, see HaloIO)
 
 struct SweepArgs {
     const float* cost;
@@ -36,46 +36,15 @@ struct SweepArgs {
     float* pathsum;
     uint16_t* disp;
     float* subpixel;
-    float* halo;     // [views][nblk][2][HALO_RING][D]
-    int* progress;   // [views][nblk] rows published by each block
-    int* error;      // set to 1 when a spin timed out
+    float* halo;     // [views][nblk][2][HALO_RING] tagged vectors (HaloIO)
+    unsigned tag_base;  // launch sequence number << 12: tags of this launch are tag_base + row + 1
+    int* error;      // set to 1 when a halo wait timed out
     int h, w;
     int view0;       // first view handled by this launch (blockIdx.y is added)
     float P1, P2, ratio;
     int min_gap;
     size_t vol_stride, img_stride;
 };
-
-__device__ __forceinline__ int ld_acquire(const int* p) {
-    int v;
-    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ void st_release(int* p, int v) {
-    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-template <int D>
-__device__ __forceinline__ void load_pixel_cg(const float* pix, int lane, float (&v)[LaneLayout<D>::E]) {
-    using LL = LaneLayout<D>;
-#pragma unroll
-    for (int q = 0; q < LL::NCH; ++q) {
-        const float* p = pix + q * LL::CHUNK_SPAN + lane * LL::CW;
-        if constexpr (LL::CW == 4) {
-            const float4 t = __ldcg(reinterpret_cast<const float4*>(p));
-            v[q * 4 + 0] = t.x;
-            v[q * 4 + 1] = t.y;
-            v[q * 4 + 2] = t.z;
-            v[q * 4 + 3] = t.w;
-        } else if constexpr (LL::CW == 2) {
-            const float2 t = __ldcg(reinterpret_cast<const float2*>(p));
-            v[q * 2 + 0] = t.x;
-            v[q * 2 + 1] = t.y;
-        } else {
-            v[q] = __ldcg(p);
-        }
-    }
-}
 
 template <int E>
 __device__ __forceinline__ float vec_min(const float (&v)[E]) {
@@ -133,170 +102,226 @@ __global__ void __launch_bounds__(128) sgm_hpair_kernel(const float* __restrict_
 }
 
 // ---------------------------------------------------------------------------------------------
+// Cross-block halo exchange without flags or fences.  A diagonal vector (D floats) that has to reach the neighbouring
+// block is written to an L2-resident ring slot as 64-bit words {value, tag}; the tag names the launch and the row, so
+// the consumer simply polls the payload itself (L1-bypassing loads) until every word carries the tag it expects.  One
+// L2 round trip per hop, nothing else on the critical path.
+//
+// Ring safety (RING >= 4): a block publishes row r+RING into the slot of row r only after it has consumed its
+// neighbour's row r+RING-2 vector, which the neighbour published after finishing row r+RING-3, i.e. after it had
+// read this block's row r+RING-4 >= r vector.
+template <int D>
+struct HaloIO {
+    static constexpr int E = LaneLayout<D>::E;
+    static constexpr int SLOT_WORDS = E * 32;  // 64-bit {value, tag} words per vector
+    // Every 64-bit word carries its own tag and is moved by 64-bit scalar (or v2.u64) accesses: however the
+    // hardware or ptxas splits an access, a word is never torn, so a value is valid iff its own tag matches.
+    __device__ static __forceinline__ unsigned long long pack(float v, unsigned tag) {
+        return (unsigned long long)__float_as_uint(v) | ((unsigned long long)tag << 32);
+    }
+    __device__ static __forceinline__ void publish(unsigned long long* slot, int lane, const float (&v)[E], unsigned tag) {
+        if constexpr (E == 1) {
+            asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(slot + lane), "l"(pack(v[0], tag)) : "memory");
+        } else {
+#pragma unroll
+            for (int q = 0; q < E / 2; ++q)
+                asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(slot + (q * 32 + lane) * 2), "l"(pack(v[2 * q], tag)),
+                             "l"(pack(v[2 * q + 1], tag))
+                             : "memory");
+        }
+    }
+    // Polls until the whole vector of `tag` has arrived; false when it timed out.
+    __device__ static __forceinline__ bool consume(const unsigned long long* slot, int lane, float (&v)[E], unsigned tag) {
+#pragma unroll 1
+        for (int spin = 0; spin < (1 << 22); ++spin) {
+            bool ok = true;
+            if constexpr (E == 1) {
+                unsigned long long x;
+                asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(x) : "l"(slot + lane) : "memory");
+                ok = (unsigned)(x >> 32) == tag;
+                v[0] = __uint_as_float((unsigned)x);
+            } else {
+#pragma unroll
+                for (int q = 0; q < E / 2; ++q) {
+                    unsigned long long x, y;
+                    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(x), "=l"(y) : "l"(slot + (q * 32 + lane) * 2) : "memory");
+                    ok = ok && (unsigned)(x >> 32) == tag && (unsigned)(y >> 32) == tag;
+                    v[2 * q] = __uint_as_float((unsigned)x);
+                    v[2 * q + 1] = __uint_as_float((unsigned)y);
+                }
+            }
+            if (__all_sync(FULL_MASK, ok)) return true;
+        }
+        return false;
+    }
+};
+
+__device__ __forceinline__ void named_barrier(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
+
+// ---------------------------------------------------------------------------------------------
 // Row-synchronous sweep.  UP == false: rows 0 -> h-1 with L3 (src/SGM.cpp:162-199), L5 and L6 (:247-305).
 //                         UP == true : rows h-1 -> 0 with L4 (:202-239), L7 and L8 (:311-369) + sum/WTA (:373-418).
-// Warp w of block b owns column j = b*NW + w.  "dl" is the diagonal whose predecessor is the LEFT neighbour column
-// (L5 going down, L7 going up), "dr" the one whose predecessor is the RIGHT neighbour column (L6 / L8).  After a row
-// every warp publishes its dl ("to the right") and dr ("to the left") vectors; the next row's neighbours pick them up.
+// Warp w of block b owns column j = b*NW + w and keeps the vertical path in registers.  "Pl" is the diagonal whose
+// predecessor is the LEFT neighbour column (L5 going down, L7 going up), "Pr" the one whose predecessor is the RIGHT
+// neighbour column (L6 / L8).  Inside a block the previous row's diagonal vectors travel through shared memory (one
+// named barrier per row); across blocks through HaloIO.  Each warp runs its two diagonals in the order
+//     F = the one a NEIGHBOURING BLOCK is waiting for (if any), published as soon as it is computed,
+//     V = the vertical path,
+//     G = the one that may have to wait for a neighbouring block,
+// so a vector is published about one row and one step before the neighbour needs it, which hides the L2 hop.
 template <int D, int NW, bool UP, int PATHS, int PF>
 __global__ void __launch_bounds__(NW * 32, (LaneLayout<D>::E >= 8) ? 2 : 3) sgm_sweep_kernel(const SweepArgs a) {
     using LL = LaneLayout<D>;
+    using HIO = HaloIO<D>;
     constexpr int E = LL::E;
     constexpr bool DIAG = PATHS == 8;
-    __shared__ __align__(16) float xch[DIAG ? 2 : 1][DIAG ? NW : 1][2][DIAG ? D : 4];
+    static_assert(NW >= 2, "a block needs two columns");
+    __shared__ __align__(16) float xch[DIAG ? 2 : 1][DIAG ? NW : 1][2][DIAG ? D : 4];  // [parity][warp][0 = Pl, 1 = Pr][d]
+    __shared__ float xmin[DIAG ? 2 : 1][DIAG ? NW : 1][2];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int blk = blockIdx.x, nblk = gridDim.x;
     const int view = a.view0 + blockIdx.y;
     const int h = a.h, w = a.w;
     const int j = blk * NW + wid;
-    const bool active = j < w;
-    const float* __restrict__ cost = a.cost + view * a.vol_stride;
-    float* acc_a = a.acc_a + view * a.vol_stride;
-    float* acc_b = (DIAG || !UP) ? a.acc_b + view * a.vol_stride : nullptr;
-    // halo ring slots: [view][blk][which][HALO_RING][D]; which 0 = "to the right" (read by blk+1), 1 = "to the left" (read by blk-1)
-    float* halo_mine = DIAG ? a.halo + ((size_t)(view * nblk + blk) * 2) * HALO_RING * D : nullptr;
-    const float* halo_left = DIAG && blk > 0 ? a.halo + ((size_t)(view * nblk + blk - 1) * 2 + 0) * HALO_RING * D : nullptr;
-    const float* halo_right = DIAG && blk + 1 < nblk ? a.halo + ((size_t)(view * nblk + blk + 1) * 2 + 1) * HALO_RING * D : nullptr;
-    int* progress = a.progress + view * nblk;
+    const int nact = min(NW, w - blk * NW);  // columns (= warps) of this block that exist
+    if (wid >= nact) return;                 // the row barrier below only counts the active warps
 
     const size_t row_stride = (size_t)w * D;
-    const size_t col_off = (size_t)(active ? j : 0) * D;
+    const float* __restrict__ cost = a.cost + view * a.vol_stride + (size_t)j * D;
+    float* acc_a = a.acc_a + view * a.vol_stride + (size_t)j * D;
+    float* acc_b = (DIAG || !UP) ? a.acc_b + view * a.vol_stride + (size_t)j * D : nullptr;
+    float* pathsum = (UP && a.pathsum) ? a.pathsum + view * a.vol_stride + (size_t)j * D : nullptr;
     auto row_of = [&](int r) { return UP ? h - 1 - r : r; };
+
+    // ---- roles of the two diagonals of this warp ----
+    const bool swap = DIAG && wid == 0 && blk > 0;  // F = Pr (the left block waits for it), G = Pl (comes from the left block)
+    const int f_id = swap ? 1 : 0, g_id = swap ? 0 : 1;
+    const bool left_border = j == 0, right_border = j == w - 1;
+    const bool f_init = swap ? right_border : left_border;   // F always starts afresh (image border on its predecessor side)
+    const bool g_init = swap ? false : right_border;
+    const int f_src_w = swap ? wid + 1 : wid - 1;             // shared-memory source warp of F
+    const bool g_global = DIAG && (swap || (wid == nact - 1 && blk + 1 < nblk));
+    const int g_src_w = swap ? 0 : wid + 1;                   // shared-memory source warp of G (unused when g_global / g_init)
+    // halo ring: [view][blk][2][RING] vectors; which 0 = right-going (Pl of the last column), 1 = left-going (Pr of column 0)
+    unsigned long long* halo = reinterpret_cast<unsigned long long*>(a.halo);
+    auto ring = [&](int b, int which) { return halo + ((size_t)(view * nblk + b) * 2 + which) * HALO_RING * HIO::SLOT_WORDS; };
+    unsigned long long* f_pub = nullptr;
+    const unsigned long long* g_sub = nullptr;
+    if (DIAG) {
+        if (swap) f_pub = ring(blk, 1);
+        else if (wid == nact - 1 && blk + 1 < nblk) f_pub = ring(blk, 0);
+        if (swap) g_sub = ring(blk - 1, 0);
+        else if (g_global) g_sub = ring(blk + 1, 1);
+    }
 
     float Cb[PF][E], Xb[PF][E], Yb[PF][E];
     auto issue = [&](int r, float (&c)[E], float (&x)[E], float (&y)[E]) {
-        const size_t off = (size_t)row_of(r) * row_stride + col_off;
+        const size_t off = (size_t)row_of(r) * row_stride;
         load_pixel_ro<D>(cost + off, lane, c);
         load_pixel<D>(acc_a + off, lane, x);
         if (DIAG || !UP) load_pixel<D>(acc_b + off, lane, y);
     };
-    if (active) {
 #pragma unroll
-        for (int u = 0; u < PF; ++u)
-            if (u < h) issue(u, Cb[u], Xb[u], Yb[u]);
-    }
+    for (int u = 0; u < PF; ++u)
+        if (u < h) issue(u, Cb[u], Xb[u], Yb[u]);
 
     float V[E];
     float mV = 0.f;
-    bool dead = false;  // set when a spin timed out: keep hitting the barriers, stop waiting
+    bool dead = false;  // a halo wait timed out: stop waiting, keep the barriers going
     for (int r0 = 0; r0 < h; r0 += PF) {
 #pragma unroll
         for (int u = 0; u < PF; ++u) {
             const int r = r0 + u;
             if (r < h) {
                 const int par = r & 1;
-                float Pl[E], Pr[E];
-                if (active) {
-                    const int i = row_of(r);
-                    // ---- predecessors of the two diagonals (previous row of the neighbour columns) ----
-                    const bool init_l = !DIAG || r == 0 || j == 0;
-                    const bool init_r = !DIAG || r == 0 || j == w - 1;
-                    if (DIAG && !init_l) {
-                        if (wid > 0) {
-                            load_pixel<D>(&xch[par ^ 1][wid - 1][0][0], lane, Pl);
-                        } else {
-                            if (lane == 0 && !dead) {
-                                const long long t0 = clock64();
-                                while (ld_acquire(progress + blk - 1) < r) {
-                                    if (clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
-                                        atomicExch(a.error, 1);
-                                        dead = true;
-                                        break;
-                                    }
-                                }
-                            }
-                            dead = __shfl_sync(FULL_MASK, (int)dead, 0) != 0;
-                            load_pixel_cg<D>(halo_left + (size_t)((r - 1) % HALO_RING) * D, lane, Pl);
-                        }
-                    }
-                    if (DIAG && !init_r) {
-                        if (wid < NW - 1) {
-                            load_pixel<D>(&xch[par ^ 1][wid + 1][1][0], lane, Pr);
-                        } else {
-                            if (lane == 0 && !dead) {
-                                const long long t0 = clock64();
-                                while (ld_acquire(progress + blk + 1) < r) {
-                                    if (clock64() - t0 > SPIN_TIMEOUT_CYCLES) {
-                                        atomicExch(a.error, 1);
-                                        dead = true;
-                                        break;
-                                    }
-                                }
-                            }
-                            dead = __shfl_sync(FULL_MASK, (int)dead, 0) != 0;
-                            load_pixel_cg<D>(halo_right + (size_t)((r - 1) % HALO_RING) * D, lane, Pr);
-                        }
-                    }
-                    // ---- the three recurrences ----
-                    if (r == 0) {
-#pragma unroll
-                        for (int k = 0; k < E; ++k) V[k] = Cb[u][k];
-                        mV = warp_min_f32(vec_min<E>(V));
-                    } else {
-                        path_step<D>(V, Cb[u], mV, lane, a.P1, a.P2);
-                    }
-                    if (DIAG) {
-                        if (init_l) {
-#pragma unroll
-                            for (int k = 0; k < E; ++k) Pl[k] = Cb[u][k];
-                        } else {
-                            float ml = warp_min_f32(vec_min<E>(Pl));
-                            path_step<D>(Pl, Cb[u], ml, lane, a.P1, a.P2);
-                        }
-                        if (init_r) {
-#pragma unroll
-                            for (int k = 0; k < E; ++k) Pr[k] = Cb[u][k];
-                        } else {
-                            float mr = warp_min_f32(vec_min<E>(Pr));
-                            path_step<D>(Pr, Cb[u], mr, lane, a.P1, a.P2);
-                        }
-                        // ---- publish for the next row's neighbours ----
-                        store_pixel<D>(&xch[par][wid][0][0], lane, Pl);
-                        store_pixel<D>(&xch[par][wid][1][0], lane, Pr);
-                        if (wid == NW - 1 && blk + 1 < nblk) store_pixel<D>(halo_mine + (size_t)(0 * HALO_RING + r % HALO_RING) * D, lane, Pl);
-                        if (wid == 0 && blk > 0) store_pixel<D>(halo_mine + (size_t)(1 * HALO_RING + r % HALO_RING) * D, lane, Pr);
-                    }
-                    // ---- outputs ----
-                    const size_t pix = (size_t)i * w + j;
-                    const size_t off = pix * D;
-                    if (!UP) {
-                        float A[E];
-#pragma unroll
-                        for (int k = 0; k < E; ++k) {
-                            A[k] = __fadd_rn(__fadd_rn(Xb[u][k], Yb[u][k]), V[k]);  // (L1 + L2) + L3
-                        }
-                        store_pixel<D>(acc_a + off, lane, A);
-                        if (DIAG) {
-                            float B[E];
-#pragma unroll
-                            for (int k = 0; k < E; ++k) B[k] = __fadd_rn(Pl[k], Pr[k]);
-                            store_pixel<D>(acc_b + off, lane, B);
-                        }
-                    } else {
-                        float S[E];
-#pragma unroll
-                        for (int k = 0; k < E; ++k) {
-                            const float sa = __fadd_rn(Xb[u][k], V[k]);
-                            S[k] = DIAG ? __fadd_rn(sa, __fadd_rn(__fadd_rn(Yb[u][k], Pl[k]), Pr[k])) : sa;
-                        }
-                        if (a.pathsum) store_pixel<D>(a.pathsum + view * a.vol_stride + off, lane, S);
-                        int dd;
-                        float sub;
-                        wta_pixel<D>(S, lane, a.ratio, a.min_gap, true, dd, sub);
-                        if (lane == 0) {
-                            a.disp[view * a.img_stride + pix] = (uint16_t)dd;
-                            a.subpixel[view * a.img_stride + pix] = sub;
-                        }
-                    }
-                    if (r + PF < h) issue(r + PF, Cb[u], Xb[u], Yb[u]);
-                }
+                const unsigned tag = a.tag_base + (unsigned)r + 1u;
+                float F[E], G[E];
+                // ---- F: first diagonal ----
                 if (DIAG) {
-                    __syncthreads();  // this row's xch / halo stores are done block-wide
-                    if (threadIdx.x == 0) {
-                        __threadfence();
-                        st_release(progress + blk, r + 1);
+                    float mF;
+                    if (r == 0 || f_init) {
+#pragma unroll
+                        for (int k = 0; k < E; ++k) F[k] = Cb[u][k];
+                        mF = warp_min_f32(vec_min<E>(F));
+                    } else {
+                        load_pixel<D>(&xch[par ^ 1][f_src_w][f_id][0], lane, F);
+                        mF = xmin[par ^ 1][f_src_w][f_id];
+                        path_step<D>(F, Cb[u], mF, lane, a.P1, a.P2);
+                    }
+                    if (f_pub) HIO::publish(f_pub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, F, tag);
+                    store_pixel<D>(&xch[par][wid][f_id][0], lane, F);
+                    if (lane == 0) xmin[par][wid][f_id] = mF;
+                }
+                // ---- V: vertical path ----
+                if (r == 0) {
+#pragma unroll
+                    for (int k = 0; k < E; ++k) V[k] = Cb[u][k];
+                    mV = warp_min_f32(vec_min<E>(V));
+                } else {
+                    path_step<D>(V, Cb[u], mV, lane, a.P1, a.P2);
+                }
+                // ---- G: second diagonal ----
+                if (DIAG) {
+                    float mG;
+                    if (r == 0 || g_init) {
+#pragma unroll
+                        for (int k = 0; k < E; ++k) G[k] = Cb[u][k];
+                        mG = warp_min_f32(vec_min<E>(G));
+                    } else {
+                        if (g_global) {
+                            if (!dead && !HIO::consume(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, G, tag - 1u)) {
+                                dead = true;
+                                if (lane == 0) atomicExch(a.error, 1);
+                            }
+                            mG = warp_min_f32(vec_min<E>(G));
+                        } else {
+                            load_pixel<D>(&xch[par ^ 1][g_src_w][g_id][0], lane, G);
+                            mG = xmin[par ^ 1][g_src_w][g_id];
+                        }
+                        path_step<D>(G, Cb[u], mG, lane, a.P1, a.P2);
+                    }
+                    store_pixel<D>(&xch[par][wid][g_id][0], lane, G);
+                    if (lane == 0) xmin[par][wid][g_id] = mG;
+                }
+                // ---- outputs ----
+                const size_t off = (size_t)row_of(r) * row_stride;
+                if (!UP) {
+                    float A[E];
+#pragma unroll
+                    for (int k = 0; k < E; ++k) A[k] = __fadd_rn(__fadd_rn(Xb[u][k], Yb[u][k]), V[k]);  // (L1 + L2) + L3
+                    store_pixel<D>(acc_a + off, lane, A);
+                    if (DIAG) {
+                        float B[E];
+#pragma unroll
+                        for (int k = 0; k < E; ++k) B[k] = __fadd_rn(F[k], G[k]);  // L5 + L6 (float add commutes)
+                        store_pixel<D>(acc_b + off, lane, B);
+                    }
+                } else {
+                    float S[E];
+                    if (!DIAG) {
+#pragma unroll
+                        for (int k = 0; k < E; ++k) S[k] = __fadd_rn(Xb[u][k], V[k]);
+                    } else if (!swap) {
+#pragma unroll
+                        for (int k = 0; k < E; ++k)  // (A + L4) + ((B + L7) + L8), src/SGM.cpp:386-390
+                            S[k] = __fadd_rn(__fadd_rn(Xb[u][k], V[k]), __fadd_rn(__fadd_rn(Yb[u][k], F[k]), G[k]));
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < E; ++k)
+                            S[k] = __fadd_rn(__fadd_rn(Xb[u][k], V[k]), __fadd_rn(__fadd_rn(Yb[u][k], G[k]), F[k]));
+                    }
+                    if (pathsum) store_pixel<D>(pathsum + off, lane, S);
+                    int dd;
+                    float sub;
+                    wta_pixel<D>(S, lane, a.ratio, a.min_gap, true, dd, sub);
+                    if (lane == 0) {
+                        const size_t pix = view * a.img_stride + (size_t)row_of(r) * w + j;
+                        a.disp[pix] = (uint16_t)dd;
+                        a.subpixel[pix] = sub;
                     }
                 }
+                if (r + PF < h) issue(r + PF, Cb[u], Xb[u], Yb[u]);
+                if (DIAG) named_barrier(1, nact * 32);  // this row's xch / xmin are complete; the other parity is free again
             }
         }
     }
@@ -352,7 +377,6 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
     sa.disp = a.disp;
     sa.subpixel = a.subpixel;
     sa.halo = a.halo;
-    sa.progress = a.progress;
     sa.error = a.error;
     sa.h = a.h;
     sa.w = a.w;
@@ -363,7 +387,12 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
     sa.vol_stride = vol;
     sa.img_stride = (size_t)a.h * a.w;
     for (int up = 0; up < 2; ++up) {
-        if (PATHS == 8) cudaMemsetAsync(a.progress, 0, sizeof(int) * (size_t)a.views * nblk, st);
+        // every sweep launch gets its own tag range; after 2^20 launches the ring is wiped and the sequence restarts
+        if (*a.launch_seq >= (1u << 20) - 1u) {
+            cudaMemsetAsync(a.halo, 0, fused_halo_bytes(a.views, a.w, a.d), st);
+            *a.launch_seq = 0;
+        }
+        sa.tag_base = ++(*a.launch_seq) << 12;
         for (int v0 = 0; v0 < a.views; v0 += views_per_launch) {
             sa.view0 = v0;
             cudaError_t e = up ? launch_sweep<D, true, PATHS>(sa, nblk, views_per_launch, PATHS == 8, st)
@@ -385,11 +414,13 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
 
 }  // namespace
 
-size_t fused_halo_floats(int views, int w, int d) { return (size_t)views * ((w + SWEEP_NW - 1) / SWEEP_NW) * 2 * HALO_RING * d; }
-size_t fused_progress_ints(int views, int w) { return (size_t)views * ((w + SWEEP_NW - 1) / SWEEP_NW); }
+size_t fused_halo_bytes(int views, int w, int d) {
+    const size_t words = (size_t)(d / 32) * 32;  // HaloIO<D>::SLOT_WORDS
+    return (size_t)views * ((w + SWEEP_NW - 1) / SWEEP_NW) * 2 * HALO_RING * words * sizeof(unsigned long long);
+}
 
 bool launch_aggregate_fused(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
-    if (!a.halo || !a.progress || !a.error || !a.acc_b) return false;
+    if (!a.halo || !a.launch_seq || !a.error || !a.acc_b || a.h > 4000) return false;
     switch (a.d) {
         case 32: return fused_dispatch<32>(a, st, lc);
         case 64: return fused_dispatch<64>(a, st, lc);
