@@ -19,6 +19,8 @@
 // neighbours' PREVIOUS row, so all blocks advance within one row of their neighbours; the kernel is launched
 // cooperatively so that every block is resident, and every wait has a time-out that raises an error flag instead of
 // hanging.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "sgm_device.cuh"
@@ -39,6 +41,7 @@ struct SweepArgs {
     float* halo;     // [views][nblk][2][HALO_RING] tagged vectors (HaloIO)
     unsigned tag_base;  // launch sequence number << 12: tags of this launch are tag_base + row + 1
     int* error;      // set to 1 when a halo wait timed out
+    int debug;       // perf experiments only (SGM_B200_SWEEP_DEBUG): 1 = skip halo waits, 2 = skip row barrier waits (WRONG results)
     int h, w;
     int view0;       // first view handled by this launch (blockIdx.y is added)
     float P1, P2, ratio;
@@ -156,52 +159,208 @@ struct HaloIO {
     }
 };
 
-__device__ __forceinline__ void named_barrier(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
+// ---- shared-memory helpers on 32-bit shared-space addresses (so that every offset folds into the instruction) ----
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+template <int D>
+__device__ __forceinline__ void lds_pixel(unsigned addr, float (&v)[LaneLayout<D>::E]) {  // addr already includes lane * CW * 4
+    using LL = LaneLayout<D>;
+#pragma unroll
+    for (int q = 0; q < LL::NCH; ++q) {
+        const unsigned p = addr + q * LL::CHUNK_SPAN * 4;
+        if constexpr (LL::CW == 4)
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v[q * 4]), "=f"(v[q * 4 + 1]), "=f"(v[q * 4 + 2]), "=f"(v[q * 4 + 3]) : "r"(p));
+        else if constexpr (LL::CW == 2)
+            asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v[q * 2]), "=f"(v[q * 2 + 1]) : "r"(p));
+        else
+            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v[q]) : "r"(p));
+    }
+}
+template <int D>
+__device__ __forceinline__ void sts_pixel(unsigned addr, const float (&v)[LaneLayout<D>::E]) {
+    using LL = LaneLayout<D>;
+#pragma unroll
+    for (int q = 0; q < LL::NCH; ++q) {
+        const unsigned p = addr + q * LL::CHUNK_SPAN * 4;
+        if constexpr (LL::CW == 4)
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(p), "f"(v[q * 4]), "f"(v[q * 4 + 1]), "f"(v[q * 4 + 2]), "f"(v[q * 4 + 3]) : "memory");
+        else if constexpr (LL::CW == 2)
+            asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(p), "f"(v[q * 2]), "f"(v[q * 2 + 1]) : "memory");
+        else
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(p), "f"(v[q]) : "memory");
+    }
+}
+__device__ __forceinline__ float lds_f32(unsigned addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void sts_f32(unsigned addr, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory"); }
+
+// Row barrier of a block as an mbarrier: a warp ARRIVES as soon as its diagonal vectors of the row are in shared memory
+// and only WAITS at the top of the next row, so the row's output work (sums, stores, WTA) overlaps the wait.
+__device__ __forceinline__ void mbar_init(unsigned bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+    asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra WAIT_DONE;\n\t"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n\t}" ::"r"(bar),
+        "r"(parity)
+        : "memory");
+}
+
+// One pixel's D values <-> registers, through a pointer that already includes the lane's offset (lane * CW floats).
+template <int D>
+__device__ __forceinline__ void ldg_ro_vec(const float* p, float (&v)[LaneLayout<D>::E]) {
+    using LL = LaneLayout<D>;
+#pragma unroll
+    for (int q = 0; q < LL::NCH; ++q) VecIO<LL::CW>::load_ro(p + q * LL::CHUNK_SPAN, &v[q * LL::CW]);
+}
+template <int D>
+__device__ __forceinline__ void ldg_vec(const float* p, float (&v)[LaneLayout<D>::E]) {
+    using LL = LaneLayout<D>;
+#pragma unroll
+    for (int q = 0; q < LL::NCH; ++q) VecIO<LL::CW>::load(p + q * LL::CHUNK_SPAN, &v[q * LL::CW]);
+}
+template <int D>
+__device__ __forceinline__ void stg_vec(float* p, const float (&v)[LaneLayout<D>::E]) {
+    using LL = LaneLayout<D>;
+#pragma unroll
+    for (int q = 0; q < LL::NCH; ++q) VecIO<LL::CW>::store(p + q * LL::CHUNK_SPAN, &v[q * LL::CW]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// L1 / L2 again, with the row streamed through a per-warp shared-memory ring by cp.async (LDGSTS) instead of register
+// prefetch.  A deep register prefetch (16 loads in flight per warp) has to share the warp's six load scoreboards, so
+// waiting for the oldest load also waits for younger ones and the effective depth collapses (measured: 1100 cycles per
+// pixel step, 2.6 TB/s, whatever the image width).  cp.async completion is tracked per commit group, so PF really
+// means PF pixels in flight, and the ring costs no registers.  Each lane copies and later reads back its own 16 bytes,
+// so no cross-lane synchronisation is needed.
+template <int BYTES>
+__device__ __forceinline__ void cp_async_lane(unsigned dst, const void* src) {
+    if constexpr (BYTES == 16)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+    else if constexpr (BYTES == 8)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+    else
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+
+template <int D, int PF, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) sgm_hpair_async_kernel(const float* __restrict__ cost, float* __restrict__ out_fwd,
+                                                                     float* __restrict__ out_bwd, int h, int w, float P1,
+                                                                     float P2, size_t vol_stride) {
+    using LL = LaneLayout<D>;
+    constexpr int E = LL::E;
+    extern __shared__ __align__(16) float hring[];  // [WARPS][PF][D]
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int row = blockIdx.x * WARPS + wid;
+    if (row >= h) return;
+    const int view = blockIdx.y;
+    const bool bwd = blockIdx.z != 0;
+    const ptrdiff_t step = bwd ? -(ptrdiff_t)D : (ptrdiff_t)D;
+    const size_t first = view * vol_stride + ((size_t)row * w + (bwd ? w - 1 : 0)) * D + lane * LL::CW;
+    const float* pc = cost + first;                      // next pixel to fetch
+    float* po = (bwd ? out_bwd : out_fwd) + first;       // next pixel to write
+    const unsigned ring = smem_u32(hring) + (unsigned)wid * PF * D * 4 + lane * LL::CW * 4;
+
+    auto fetch = [&](int slot) {
+#pragma unroll
+        for (int q = 0; q < LL::NCH; ++q) cp_async_lane<LL::CW * 4>(ring + slot * D * 4 + q * LL::CHUNK_SPAN * 4, pc + q * LL::CHUNK_SPAN);
+        pc += step;
+    };
+#pragma unroll
+    for (int u = 0; u < PF; ++u) {
+        if (u < w) fetch(u);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+
+    float L[E];
+    float m = 0.f;
+    for (int s0 = 0; s0 < w; s0 += PF) {
+#pragma unroll
+        for (int u = 0; u < PF; ++u) {
+            const int s = s0 + u;
+            if (s < w) {
+                asm volatile("cp.async.wait_group %0;" ::"n"(PF - 1) : "memory");  // the group of pixel s has landed
+                float C[E];
+                lds_pixel<D>(ring + u * D * 4, C);
+                if (s == 0) {
+#pragma unroll
+                    for (int k = 0; k < E; ++k) L[k] = C[k];
+                    m = warp_min_f32(vec_min<E>(L));
+                } else {
+                    path_step<D>(L, C, m, lane, P1, P2);
+                }
+                stg_vec<D>(po, L);
+                po += step;
+                if (s + PF < w) fetch(u);  // slot u is free again: the lane has read its own bytes back
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            }
+        }
+    }
+}
 
 // ---------------------------------------------------------------------------------------------
 // Row-synchronous sweep.  UP == false: rows 0 -> h-1 with L3 (src/SGM.cpp:162-199), L5 and L6 (:247-305).
 //                         UP == true : rows h-1 -> 0 with L4 (:202-239), L7 and L8 (:311-369) + sum/WTA (:373-418).
 // Warp w of block b owns column j = b*NW + w and keeps the vertical path in registers.  "Pl" is the diagonal whose
 // predecessor is the LEFT neighbour column (L5 going down, L7 going up), "Pr" the one whose predecessor is the RIGHT
-// neighbour column (L6 / L8).  Inside a block the previous row's diagonal vectors travel through shared memory (one
-// named barrier per row); across blocks through HaloIO.  Each warp runs its two diagonals in the order
+// neighbour column (L6 / L8).  Inside a block the previous row's diagonal vectors travel through shared memory (double
+// buffered by row parity, one mbarrier phase per row); across blocks through HaloIO.  Each warp runs its two diagonals
+// in the order
 //     F = the one a NEIGHBOURING BLOCK is waiting for (if any), published as soon as it is computed,
 //     V = the vertical path,
 //     G = the one that may have to wait for a neighbouring block,
 // so a vector is published about one row and one step before the neighbour needs it, which hides the L2 hop.
-template <int D, int NW, bool UP, int PATHS, int PF>
-__global__ void __launch_bounds__(NW * 32, (LaneLayout<D>::E >= 8) ? 2 : 3) sgm_sweep_kernel(const SweepArgs a) {
+// PF (rows of C / A / B kept in flight per warp) is even, so the row parity is a compile-time constant of the
+// unrolled body and every shared-memory address is base + immediate.
+template <int D, int NW, bool UP, int PATHS, int PF, int MINB>
+__global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArgs a) {
     using LL = LaneLayout<D>;
     using HIO = HaloIO<D>;
     constexpr int E = LL::E;
     constexpr bool DIAG = PATHS == 8;
-    static_assert(NW >= 2, "a block needs two columns");
-    __shared__ __align__(16) float xch[DIAG ? 2 : 1][DIAG ? NW : 1][2][DIAG ? D : 4];  // [parity][warp][0 = Pl, 1 = Pr][d]
-    __shared__ float xmin[DIAG ? 2 : 1][DIAG ? NW : 1][2];
+    static_assert(NW >= 2 && PF % 2 == 0, "a block needs two columns; PF must be even");
+    constexpr unsigned VEC_BYTES = D * 4, WARP_BYTES = 2 * VEC_BYTES, PAR_BYTES = NW * WARP_BYTES, MIN_PAR_BYTES = NW * 2 * 4;
+    __shared__ __align__(16) float xch[DIAG ? 2 * NW * 2 * D : 4];  // [parity][warp][0 = Pl, 1 = Pr][d]
+    __shared__ float xmin[DIAG ? 2 * NW * 2 : 1];                   // [parity][warp][0 = Pl, 1 = Pr] min of the vector
+    __shared__ __align__(8) unsigned long long bar_mem;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int blk = blockIdx.x, nblk = gridDim.x;
     const int view = a.view0 + blockIdx.y;
     const int h = a.h, w = a.w;
     const int j = blk * NW + wid;
     const int nact = min(NW, w - blk * NW);  // columns (= warps) of this block that exist
-    if (wid >= nact) return;                 // the row barrier below only counts the active warps
-
-    const size_t row_stride = (size_t)w * D;
-    const float* __restrict__ cost = a.cost + view * a.vol_stride + (size_t)j * D;
-    float* acc_a = a.acc_a + view * a.vol_stride + (size_t)j * D;
-    float* acc_b = (DIAG || !UP) ? a.acc_b + view * a.vol_stride + (size_t)j * D : nullptr;
-    float* pathsum = (UP && a.pathsum) ? a.pathsum + view * a.vol_stride + (size_t)j * D : nullptr;
-    auto row_of = [&](int r) { return UP ? h - 1 - r : r; };
+    const unsigned bar = smem_u32(&bar_mem);
+    if (DIAG) {
+        if (threadIdx.x == 0) mbar_init(bar, nact);  // one arrival per active warp and row
+        __syncthreads();
+    }
+    if (wid >= nact) return;
 
     // ---- roles of the two diagonals of this warp ----
     const bool swap = DIAG && wid == 0 && blk > 0;  // F = Pr (the left block waits for it), G = Pl (comes from the left block)
     const int f_id = swap ? 1 : 0, g_id = swap ? 0 : 1;
     const bool left_border = j == 0, right_border = j == w - 1;
-    const bool f_init = swap ? right_border : left_border;   // F always starts afresh (image border on its predecessor side)
+    const bool f_init = swap ? right_border : left_border;  // F restarts on every row (image border on its predecessor side)
     const bool g_init = swap ? false : right_border;
-    const int f_src_w = swap ? wid + 1 : wid - 1;             // shared-memory source warp of F
+    const int f_src_w = swap ? wid + 1 : wid - 1;            // shared-memory source warp of F
     const bool g_global = DIAG && (swap || (wid == nact - 1 && blk + 1 < nblk));
-    const int g_src_w = swap ? 0 : wid + 1;                   // shared-memory source warp of G (unused when g_global / g_init)
+    const int g_src_w = swap ? 0 : wid + 1;                  // shared-memory source warp of G (unused when g_global / g_init)
+    const unsigned lane_off = lane * LL::CW * 4;
+    const unsigned x0 = smem_u32(xch), m0 = smem_u32(xmin);
+    const unsigned f_src = x0 + f_src_w * WARP_BYTES + f_id * VEC_BYTES + lane_off, fm_src = m0 + (f_src_w * 2 + f_id) * 4;
+    const unsigned g_src = x0 + g_src_w * WARP_BYTES + g_id * VEC_BYTES + lane_off, gm_src = m0 + (g_src_w * 2 + g_id) * 4;
+    const unsigned f_dst = x0 + wid * WARP_BYTES + f_id * VEC_BYTES + lane_off, fm_dst = m0 + (wid * 2 + f_id) * 4;
+    const unsigned g_dst = x0 + wid * WARP_BYTES + g_id * VEC_BYTES + lane_off, gm_dst = m0 + (wid * 2 + g_id) * 4;
     // halo ring: [view][blk][2][RING] vectors; which 0 = right-going (Pl of the last column), 1 = left-going (Pr of column 0)
     unsigned long long* halo = reinterpret_cast<unsigned long long*>(a.halo);
     auto ring = [&](int b, int which) { return halo + ((size_t)(view * nblk + b) * 2 + which) * HALO_RING * HIO::SLOT_WORDS; };
@@ -214,28 +373,43 @@ __global__ void __launch_bounds__(NW * 32, (LaneLayout<D>::E >= 8) ? 2 : 3) sgm_
         else if (g_global) g_sub = ring(blk + 1, 1);
     }
 
+    // ---- global pointers: p* run PF rows ahead (prefetch), o* are at the row being finished ----
+    const ptrdiff_t rstep = UP ? -(ptrdiff_t)w * D : (ptrdiff_t)w * D;
+    const size_t first = ((size_t)(UP ? h - 1 : 0) * w + j) * D + lane * LL::CW;
+    const float* pc = a.cost + view * a.vol_stride + first;
+    const float* px = a.acc_a + view * a.vol_stride + first;
+    const float* py = (DIAG || !UP) ? a.acc_b + view * a.vol_stride + first : nullptr;
+    float* oa = a.acc_a + view * a.vol_stride + first;
+    float* ob = (DIAG && !UP) ? a.acc_b + view * a.vol_stride + first : nullptr;
+    float* os = (UP && a.pathsum) ? a.pathsum + view * a.vol_stride + first : nullptr;
+    const ptrdiff_t pstep = UP ? -(ptrdiff_t)w : (ptrdiff_t)w;
+    size_t opix = view * a.img_stride + (size_t)(UP ? h - 1 : 0) * w + j;
+
     float Cb[PF][E], Xb[PF][E], Yb[PF][E];
-    auto issue = [&](int r, float (&c)[E], float (&x)[E], float (&y)[E]) {
-        const size_t off = (size_t)row_of(r) * row_stride;
-        load_pixel_ro<D>(cost + off, lane, c);
-        load_pixel<D>(acc_a + off, lane, x);
-        if (DIAG || !UP) load_pixel<D>(acc_b + off, lane, y);
+    auto issue = [&](float (&c)[E], float (&x)[E], float (&y)[E]) {
+        ldg_ro_vec<D>(pc, c);
+        ldg_vec<D>(px, x);
+        if (DIAG || !UP) ldg_vec<D>(py, y);
+        pc += rstep;
+        px += rstep;
+        if (DIAG || !UP) py += rstep;
     };
 #pragma unroll
     for (int u = 0; u < PF; ++u)
-        if (u < h) issue(u, Cb[u], Xb[u], Yb[u]);
+        if (u < h) issue(Cb[u], Xb[u], Yb[u]);
 
     float V[E];
     float mV = 0.f;
-    bool dead = false;  // a halo wait timed out: stop waiting, keep the barriers going
+    bool dead = false;  // a halo wait timed out: stop waiting, keep the barrier phases going
     for (int r0 = 0; r0 < h; r0 += PF) {
 #pragma unroll
         for (int u = 0; u < PF; ++u) {
             const int r = r0 + u;
             if (r < h) {
-                const int par = r & 1;
+                const unsigned par = u & 1;  // == r & 1 because PF is even: a constant of the unrolled body
                 const unsigned tag = a.tag_base + (unsigned)r + 1u;
                 float F[E], G[E];
+                if (DIAG && r > 0 && !(a.debug & 2)) mbar_wait(bar, par ^ 1u);  // every warp's row r-1 vectors are in shared memory
                 // ---- F: first diagonal ----
                 if (DIAG) {
                     float mF;
@@ -244,13 +418,13 @@ __global__ void __launch_bounds__(NW * 32, (LaneLayout<D>::E >= 8) ? 2 : 3) sgm_
                         for (int k = 0; k < E; ++k) F[k] = Cb[u][k];
                         mF = warp_min_f32(vec_min<E>(F));
                     } else {
-                        load_pixel<D>(&xch[par ^ 1][f_src_w][f_id][0], lane, F);
-                        mF = xmin[par ^ 1][f_src_w][f_id];
+                        lds_pixel<D>(f_src + (par ^ 1u) * PAR_BYTES, F);
+                        mF = lds_f32(fm_src + (par ^ 1u) * MIN_PAR_BYTES);
                         path_step<D>(F, Cb[u], mF, lane, a.P1, a.P2);
                     }
                     if (f_pub) HIO::publish(f_pub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, F, tag);
-                    store_pixel<D>(&xch[par][wid][f_id][0], lane, F);
-                    if (lane == 0) xmin[par][wid][f_id] = mF;
+                    sts_pixel<D>(f_dst + par * PAR_BYTES, F);
+                    if (lane == 0) sts_f32(fm_dst + par * MIN_PAR_BYTES, mF);
                 }
                 // ---- V: vertical path ----
                 if (r == 0) {
@@ -269,33 +443,36 @@ __global__ void __launch_bounds__(NW * 32, (LaneLayout<D>::E >= 8) ? 2 : 3) sgm_
                         mG = warp_min_f32(vec_min<E>(G));
                     } else {
                         if (g_global) {
-                            if (!dead && !HIO::consume(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, G, tag - 1u)) {
+                            if (!dead && !(a.debug & 1) && !HIO::consume(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, G, tag - 1u)) {
                                 dead = true;
                                 if (lane == 0) atomicExch(a.error, 1);
                             }
                             mG = warp_min_f32(vec_min<E>(G));
                         } else {
-                            load_pixel<D>(&xch[par ^ 1][g_src_w][g_id][0], lane, G);
-                            mG = xmin[par ^ 1][g_src_w][g_id];
+                            lds_pixel<D>(g_src + (par ^ 1u) * PAR_BYTES, G);
+                            mG = lds_f32(gm_src + (par ^ 1u) * MIN_PAR_BYTES);
                         }
                         path_step<D>(G, Cb[u], mG, lane, a.P1, a.P2);
                     }
-                    store_pixel<D>(&xch[par][wid][g_id][0], lane, G);
-                    if (lane == 0) xmin[par][wid][g_id] = mG;
+                    sts_pixel<D>(g_dst + par * PAR_BYTES, G);
+                    if (lane == 0) sts_f32(gm_dst + par * MIN_PAR_BYTES, mG);
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar);  // this warp's row r vectors are published
                 }
-                // ---- outputs ----
-                const size_t off = (size_t)row_of(r) * row_stride;
+                // ---- outputs (overlap the other warps' arrival) ----
                 if (!UP) {
                     float A[E];
 #pragma unroll
                     for (int k = 0; k < E; ++k) A[k] = __fadd_rn(__fadd_rn(Xb[u][k], Yb[u][k]), V[k]);  // (L1 + L2) + L3
-                    store_pixel<D>(acc_a + off, lane, A);
+                    stg_vec<D>(oa, A);
                     if (DIAG) {
                         float B[E];
 #pragma unroll
                         for (int k = 0; k < E; ++k) B[k] = __fadd_rn(F[k], G[k]);  // L5 + L6 (float add commutes)
-                        store_pixel<D>(acc_b + off, lane, B);
+                        stg_vec<D>(ob, B);
+                        ob += rstep;
                     }
+                    oa += rstep;
                 } else {
                     float S[E];
                     if (!DIAG) {
@@ -310,64 +487,81 @@ __global__ void __launch_bounds__(NW * 32, (LaneLayout<D>::E >= 8) ? 2 : 3) sgm_
                         for (int k = 0; k < E; ++k)
                             S[k] = __fadd_rn(__fadd_rn(Xb[u][k], V[k]), __fadd_rn(__fadd_rn(Yb[u][k], G[k]), F[k]));
                     }
-                    if (pathsum) store_pixel<D>(pathsum + off, lane, S);
+                    if (os) {
+                        stg_vec<D>(os, S);
+                        os += rstep;
+                    }
                     int dd;
                     float sub;
                     wta_pixel<D>(S, lane, a.ratio, a.min_gap, true, dd, sub);
                     if (lane == 0) {
-                        const size_t pix = view * a.img_stride + (size_t)row_of(r) * w + j;
-                        a.disp[pix] = (uint16_t)dd;
-                        a.subpixel[pix] = sub;
+                        a.disp[opix] = (uint16_t)dd;
+                        a.subpixel[opix] = sub;
                     }
+                    opix += pstep;
                 }
-                if (r + PF < h) issue(r + PF, Cb[u], Xb[u], Yb[u]);
-                if (DIAG) named_barrier(1, nact * 32);  // this row's xch / xmin are complete; the other parity is free again
+                if (r + PF < h) issue(Cb[u], Xb[u], Yb[u]);
             }
         }
     }
 }
 
-constexpr int SWEEP_NW = 8;
+constexpr int SWEEP_NW = 8;  // smallest block width in columns (sizes the halo ring)
 
-template <int D, bool UP, int PATHS>
+// Launch shape of the sweeps: NW columns (warps) per block, PF rows in flight per warp, MINB blocks per SM.
+template <int NW_, int PF_, int MINB_>
+struct SweepCfg {
+    static constexpr int NW = NW_, PF = PF_, MINB = MINB_;
+};
+
+template <int D, bool UP, int PATHS, class CFG>
 cudaError_t launch_sweep(const SweepArgs& sa, int nblk, int views, bool cooperative, cudaStream_t st) {
-    constexpr int PF = (LaneLayout<D>::E >= 8) ? 2 : 3;
-    auto kern = sgm_sweep_kernel<D, SWEEP_NW, UP, PATHS, PF>;
+    auto kern = sgm_sweep_kernel<D, CFG::NW, UP, PATHS, CFG::PF, CFG::MINB>;
     if (!cooperative) {
-        kern<<<dim3(nblk, views), SWEEP_NW * 32, 0, st>>>(sa);
+        kern<<<dim3(nblk, views), CFG::NW * 32, 0, st>>>(sa);
         return cudaGetLastError();
     }
     void* params[] = {const_cast<SweepArgs*>(&sa)};
-    return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(nblk, views), dim3(SWEEP_NW * 32), params, 0, st);
+    return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(nblk, views), dim3(CFG::NW * 32), params, 0, st);
 }
 
-template <int D, int PATHS>
+template <int D, int PATHS, class CFG>
 int sweep_capacity(int device) {
-    constexpr int PF = (LaneLayout<D>::E >= 8) ? 2 : 3;
+    static int cached[16] = {};  // per device; the answer only depends on the kernel and the device
+    if (device >= 0 && device < 16 && cached[device]) return cached[device] - 1;
     int per_sm_dn = 0, per_sm_up = 0, sms = 0, coop = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_dn, sgm_sweep_kernel<D, SWEEP_NW, false, PATHS, PF>, SWEEP_NW * 32, 0);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_up, sgm_sweep_kernel<D, SWEEP_NW, true, PATHS, PF>, SWEEP_NW * 32, 0);
-    if (!coop) return 0;
-    return sms * (per_sm_dn < per_sm_up ? per_sm_dn : per_sm_up);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_dn, sgm_sweep_kernel<D, CFG::NW, false, PATHS, CFG::PF, CFG::MINB>, CFG::NW * 32, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_up, sgm_sweep_kernel<D, CFG::NW, true, PATHS, CFG::PF, CFG::MINB>, CFG::NW * 32, 0);
+    const int cap = coop ? sms * (per_sm_dn < per_sm_up ? per_sm_dn : per_sm_up) : 0;
+    if (device >= 0 && device < 16) cached[device] = cap + 1;
+    return cap;
 }
 
-template <int D, int PATHS>
+template <int D, int PATHS, class CFG>
 bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
-    const int nblk = (a.w + SWEEP_NW - 1) / SWEEP_NW;
+    const int nblk = (a.w + CFG::NW - 1) / CFG::NW;
     int views_per_launch = a.views;
     if (PATHS == 8) {
         int device = 0;
         cudaGetDevice(&device);
-        const int cap = sweep_capacity<D, PATHS>(device);
+        const int cap = sweep_capacity<D, PATHS, CFG>(device);
         if (nblk * a.views > cap) views_per_launch = 1;
         if (nblk > cap) return false;  // image too wide for a resident row-synchronous sweep: caller falls back to line walkers
     }
     const size_t vol = (size_t)a.h * a.w * a.d;
-    constexpr int PFH = (LaneLayout<D>::E >= 8) ? 8 : 16;
-    sgm_hpair_kernel<D, PFH><<<dim3((a.h + 3) / 4, a.views, 2), 128, 0, st>>>(a.cost, a.acc_a, a.acc_b, a.h, a.w, a.P1, a.P2, vol);
-    lc.note("sgm_hpair_kernel");
+    {
+        constexpr int PFH = (LaneLayout<D>::E >= 8) ? 8 : 16, HW = 4;
+        constexpr size_t ring_bytes = (size_t)HW * PFH * D * sizeof(float);  // 32 KB for D >= 128
+        static const bool legacy = std::getenv("SGM_B200_HPAIR_LEGACY") != nullptr;
+        if (legacy)
+            sgm_hpair_kernel<D, PFH><<<dim3((a.h + 3) / 4, a.views, 2), 128, 0, st>>>(a.cost, a.acc_a, a.acc_b, a.h, a.w, a.P1, a.P2, vol);
+        else
+            sgm_hpair_async_kernel<D, PFH, HW><<<dim3((a.h + HW - 1) / HW, a.views, 2), HW * 32, ring_bytes, st>>>(
+                a.cost, a.acc_a, a.acc_b, a.h, a.w, a.P1, a.P2, vol);
+        lc.note("sgm_hpair_kernel");
+    }
 
     SweepArgs sa;
     sa.cost = a.cost;
@@ -378,6 +572,10 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
     sa.subpixel = a.subpixel;
     sa.halo = a.halo;
     sa.error = a.error;
+    {
+        static const int dbg = [] { const char* e = std::getenv("SGM_B200_SWEEP_DEBUG"); return e ? std::atoi(e) : 0; }();
+        sa.debug = dbg;
+    }
     sa.h = a.h;
     sa.w = a.w;
     sa.P1 = a.P1;
@@ -395,8 +593,8 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
         sa.tag_base = ++(*a.launch_seq) << 12;
         for (int v0 = 0; v0 < a.views; v0 += views_per_launch) {
             sa.view0 = v0;
-            cudaError_t e = up ? launch_sweep<D, true, PATHS>(sa, nblk, views_per_launch, PATHS == 8, st)
-                               : launch_sweep<D, false, PATHS>(sa, nblk, views_per_launch, PATHS == 8, st);
+            cudaError_t e = up ? launch_sweep<D, true, PATHS, CFG>(sa, nblk, views_per_launch, PATHS == 8, st)
+                               : launch_sweep<D, false, PATHS, CFG>(sa, nblk, views_per_launch, PATHS == 8, st);
             if (e != cudaSuccess && lc.err == cudaSuccess) {
                 lc.err = e;
                 lc.failed = "sgm_sweep_kernel (launch)";
@@ -407,9 +605,33 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
     return true;
 }
 
+// Default shapes per D; SGM_B200_SWEEP_CFG=<n> selects an alternative for D = 128, 8 paths (tuning knob).
+template <int D>
+struct DefaultCfg {
+    using type = SweepCfg<8, (LaneLayout<D>::E >= 4) ? 2 : 4, (LaneLayout<D>::E >= 8) ? 2 : 3>;
+};
+template <>
+struct DefaultCfg<128> {
+    using type = SweepCfg<10, 2, 2>;  // measured best on 1242x375 (250 blocks of 10 columns, 2 per SM, 96 registers)
+};
+
 template <int D>
 bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
-    return a.paths == 8 ? fused_impl<D, 8>(a, st, lc) : fused_impl<D, 4>(a, st, lc);
+    if (a.paths != 8) return fused_impl<D, 4, typename DefaultCfg<D>::type>(a, st, lc);
+    if constexpr (D == 128) {
+        static const int cfg = [] {
+            const char* e = std::getenv("SGM_B200_SWEEP_CFG");
+            return e ? std::atoi(e) : 0;
+        }();
+        switch (cfg) {
+            case 1: return fused_impl<D, 8, SweepCfg<8, 4, 3>>(a, st, lc);
+            case 2: return fused_impl<D, 8, SweepCfg<10, 4, 2>>(a, st, lc);
+            case 3: return fused_impl<D, 8, SweepCfg<8, 2, 3>>(a, st, lc);
+            case 4: return fused_impl<D, 8, SweepCfg<9, 4, 2>>(a, st, lc);
+            default: break;
+        }
+    }
+    return fused_impl<D, 8, typename DefaultCfg<D>::type>(a, st, lc);
 }
 
 }  // namespace
