@@ -385,18 +385,28 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
     const ptrdiff_t pstep = UP ? -(ptrdiff_t)w : (ptrdiff_t)w;
     size_t opix = view * a.img_stride + (size_t)(UP ? h - 1 : 0) * w + j;
 
-    float Cb[PF][E], Xb[PF][E], Yb[PF][E];
-    auto issue = [&](float (&c)[E], float (&x)[E], float (&y)[E]) {
-        ldg_ro_vec<D>(pc, c);
-        ldg_vec<D>(px, x);
-        if (DIAG || !UP) ldg_vec<D>(py, y);
+    // C / A / B rows stream through a per-warp shared-memory ring filled by cp.async: PF rows in flight per warp cost no
+    // registers and are tracked per commit group (a deep register prefetch would alias the load scoreboards).
+    extern __shared__ __align__(16) float sring[];  // [NW][PF][3][D]
+    constexpr unsigned SLOT_BYTES = 3 * VEC_BYTES;
+    const unsigned rbase = smem_u32(sring) + (unsigned)wid * PF * SLOT_BYTES + lane_off;
+    auto fetch = [&](int slot) {
+#pragma unroll
+        for (int q = 0; q < LL::NCH; ++q) {
+            const unsigned dst = rbase + slot * SLOT_BYTES + q * LL::CHUNK_SPAN * 4;
+            cp_async_lane<LL::CW * 4>(dst, pc + q * LL::CHUNK_SPAN);
+            cp_async_lane<LL::CW * 4>(dst + VEC_BYTES, px + q * LL::CHUNK_SPAN);
+            if (DIAG || !UP) cp_async_lane<LL::CW * 4>(dst + 2 * VEC_BYTES, py + q * LL::CHUNK_SPAN);
+        }
         pc += rstep;
         px += rstep;
         if (DIAG || !UP) py += rstep;
     };
 #pragma unroll
-    for (int u = 0; u < PF; ++u)
-        if (u < h) issue(Cb[u], Xb[u], Yb[u]);
+    for (int u = 0; u < PF; ++u) {
+        if (u < h) fetch(u);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
 
     float V[E];
     float mV = 0.f;
@@ -408,19 +418,21 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
             if (r < h) {
                 const unsigned par = u & 1;  // == r & 1 because PF is even: a constant of the unrolled body
                 const unsigned tag = a.tag_base + (unsigned)r + 1u;
-                float F[E], G[E];
+                float F[E], G[E], C[E];
+                asm volatile("cp.async.wait_group %0;" ::"n"(PF - 1) : "memory");  // this row's C / A / B have landed
+                lds_pixel<D>(rbase + u * SLOT_BYTES, C);
                 if (DIAG && r > 0 && !(a.debug & 2)) mbar_wait(bar, par ^ 1u);  // every warp's row r-1 vectors are in shared memory
                 // ---- F: first diagonal ----
                 if (DIAG) {
                     float mF;
                     if (r == 0 || f_init) {
 #pragma unroll
-                        for (int k = 0; k < E; ++k) F[k] = Cb[u][k];
+                        for (int k = 0; k < E; ++k) F[k] = C[k];
                         mF = warp_min_f32(vec_min<E>(F));
                     } else {
                         lds_pixel<D>(f_src + (par ^ 1u) * PAR_BYTES, F);
                         mF = lds_f32(fm_src + (par ^ 1u) * MIN_PAR_BYTES);
-                        path_step<D>(F, Cb[u], mF, lane, a.P1, a.P2);
+                        path_step<D>(F, C, mF, lane, a.P1, a.P2);
                     }
                     if (f_pub) HIO::publish(f_pub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, F, tag);
                     sts_pixel<D>(f_dst + par * PAR_BYTES, F);
@@ -429,17 +441,17 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                 // ---- V: vertical path ----
                 if (r == 0) {
 #pragma unroll
-                    for (int k = 0; k < E; ++k) V[k] = Cb[u][k];
+                    for (int k = 0; k < E; ++k) V[k] = C[k];
                     mV = warp_min_f32(vec_min<E>(V));
                 } else {
-                    path_step<D>(V, Cb[u], mV, lane, a.P1, a.P2);
+                    path_step<D>(V, C, mV, lane, a.P1, a.P2);
                 }
                 // ---- G: second diagonal ----
                 if (DIAG) {
                     float mG;
                     if (r == 0 || g_init) {
 #pragma unroll
-                        for (int k = 0; k < E; ++k) G[k] = Cb[u][k];
+                        for (int k = 0; k < E; ++k) G[k] = C[k];
                         mG = warp_min_f32(vec_min<E>(G));
                     } else {
                         if (g_global) {
@@ -452,7 +464,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                             lds_pixel<D>(g_src + (par ^ 1u) * PAR_BYTES, G);
                             mG = lds_f32(gm_src + (par ^ 1u) * MIN_PAR_BYTES);
                         }
-                        path_step<D>(G, Cb[u], mG, lane, a.P1, a.P2);
+                        path_step<D>(G, C, mG, lane, a.P1, a.P2);
                     }
                     sts_pixel<D>(g_dst + par * PAR_BYTES, G);
                     if (lane == 0) sts_f32(gm_dst + par * MIN_PAR_BYTES, mG);
@@ -460,10 +472,13 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                     if (lane == 0) mbar_arrive(bar);  // this warp's row r vectors are published
                 }
                 // ---- outputs (overlap the other warps' arrival) ----
+                float X[E], Y[E];
+                lds_pixel<D>(rbase + u * SLOT_BYTES + VEC_BYTES, X);
+                if (DIAG || !UP) lds_pixel<D>(rbase + u * SLOT_BYTES + 2 * VEC_BYTES, Y);
                 if (!UP) {
                     float A[E];
 #pragma unroll
-                    for (int k = 0; k < E; ++k) A[k] = __fadd_rn(__fadd_rn(Xb[u][k], Yb[u][k]), V[k]);  // (L1 + L2) + L3
+                    for (int k = 0; k < E; ++k) A[k] = __fadd_rn(__fadd_rn(X[k], Y[k]), V[k]);  // (L1 + L2) + L3
                     stg_vec<D>(oa, A);
                     if (DIAG) {
                         float B[E];
@@ -477,15 +492,15 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                     float S[E];
                     if (!DIAG) {
 #pragma unroll
-                        for (int k = 0; k < E; ++k) S[k] = __fadd_rn(Xb[u][k], V[k]);
+                        for (int k = 0; k < E; ++k) S[k] = __fadd_rn(X[k], V[k]);
                     } else if (!swap) {
 #pragma unroll
                         for (int k = 0; k < E; ++k)  // (A + L4) + ((B + L7) + L8), src/SGM.cpp:386-390
-                            S[k] = __fadd_rn(__fadd_rn(Xb[u][k], V[k]), __fadd_rn(__fadd_rn(Yb[u][k], F[k]), G[k]));
+                            S[k] = __fadd_rn(__fadd_rn(X[k], V[k]), __fadd_rn(__fadd_rn(Y[k], F[k]), G[k]));
                     } else {
 #pragma unroll
                         for (int k = 0; k < E; ++k)
-                            S[k] = __fadd_rn(__fadd_rn(Xb[u][k], V[k]), __fadd_rn(__fadd_rn(Yb[u][k], G[k]), F[k]));
+                            S[k] = __fadd_rn(__fadd_rn(X[k], V[k]), __fadd_rn(__fadd_rn(Y[k], G[k]), F[k]));
                     }
                     if (os) {
                         stg_vec<D>(os, S);
@@ -500,7 +515,8 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                     }
                     opix += pstep;
                 }
-                if (r + PF < h) issue(Cb[u], Xb[u], Yb[u]);
+                if (r + PF < h) fetch(u);  // slot u is free: this lane has read its own bytes back
+                asm volatile("cp.async.commit_group;" ::: "memory");
             }
         }
     }
@@ -514,15 +530,23 @@ struct SweepCfg {
     static constexpr int NW = NW_, PF = PF_, MINB = MINB_;
 };
 
+template <int D, class CFG>
+constexpr size_t sweep_ring_bytes() {
+    return (size_t)CFG::NW * CFG::PF * 3 * D * sizeof(float);
+}
+
 template <int D, bool UP, int PATHS, class CFG>
 cudaError_t launch_sweep(const SweepArgs& sa, int nblk, int views, bool cooperative, cudaStream_t st) {
     auto kern = sgm_sweep_kernel<D, CFG::NW, UP, PATHS, CFG::PF, CFG::MINB>;
+    constexpr size_t ring_bytes = sweep_ring_bytes<D, CFG>();
+    cudaError_t attr = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes);  // per device: cheap, so always
+    if (attr != cudaSuccess) return attr;
     if (!cooperative) {
-        kern<<<dim3(nblk, views), CFG::NW * 32, 0, st>>>(sa);
+        kern<<<dim3(nblk, views), CFG::NW * 32, ring_bytes, st>>>(sa);
         return cudaGetLastError();
     }
     void* params[] = {const_cast<SweepArgs*>(&sa)};
-    return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(nblk, views), dim3(CFG::NW * 32), params, 0, st);
+    return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(nblk, views), dim3(CFG::NW * 32), params, ring_bytes, st);
 }
 
 template <int D, int PATHS, class CFG>
@@ -530,10 +554,15 @@ int sweep_capacity(int device) {
     static int cached[16] = {};  // per device; the answer only depends on the kernel and the device
     if (device >= 0 && device < 16 && cached[device]) return cached[device] - 1;
     int per_sm_dn = 0, per_sm_up = 0, sms = 0, coop = 0;
+    // the ring may exceed the default 48 KB of dynamic shared memory: opt in before asking for the occupancy
+    cudaFuncSetAttribute(sgm_sweep_kernel<D, CFG::NW, false, PATHS, CFG::PF, CFG::MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)sweep_ring_bytes<D, CFG>());
+    cudaFuncSetAttribute(sgm_sweep_kernel<D, CFG::NW, true, PATHS, CFG::PF, CFG::MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)sweep_ring_bytes<D, CFG>());
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_dn, sgm_sweep_kernel<D, CFG::NW, false, PATHS, CFG::PF, CFG::MINB>, CFG::NW * 32, 0);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_up, sgm_sweep_kernel<D, CFG::NW, true, PATHS, CFG::PF, CFG::MINB>, CFG::NW * 32, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_dn, sgm_sweep_kernel<D, CFG::NW, false, PATHS, CFG::PF, CFG::MINB>, CFG::NW * 32, sweep_ring_bytes<D, CFG>());
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_up, sgm_sweep_kernel<D, CFG::NW, true, PATHS, CFG::PF, CFG::MINB>, CFG::NW * 32, sweep_ring_bytes<D, CFG>());
     const int cap = coop ? sms * (per_sm_dn < per_sm_up ? per_sm_dn : per_sm_up) : 0;
     if (device >= 0 && device < 16) cached[device] = cap + 1;
     return cap;
@@ -612,7 +641,7 @@ struct DefaultCfg {
 };
 template <>
 struct DefaultCfg<128> {
-    using type = SweepCfg<10, 2, 2>;  // measured best on 1242x375 (250 blocks of 10 columns, 2 per SM, 96 registers)
+    using type = SweepCfg<10, 4, 2>;  // 1242x375: 250 blocks of 10 columns, 2 per SM
 };
 
 template <int D>
@@ -625,9 +654,9 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
         }();
         switch (cfg) {
             case 1: return fused_impl<D, 8, SweepCfg<8, 4, 3>>(a, st, lc);
-            case 2: return fused_impl<D, 8, SweepCfg<10, 4, 2>>(a, st, lc);
-            case 3: return fused_impl<D, 8, SweepCfg<8, 2, 3>>(a, st, lc);
-            case 4: return fused_impl<D, 8, SweepCfg<9, 4, 2>>(a, st, lc);
+            case 2: return fused_impl<D, 8, SweepCfg<10, 6, 2>>(a, st, lc);
+            case 3: return fused_impl<D, 8, SweepCfg<10, 2, 2>>(a, st, lc);
+            case 4: return fused_impl<D, 8, SweepCfg<12, 4, 2>>(a, st, lc);
             default: break;
         }
     }
