@@ -4,6 +4,8 @@
 //
 // Replaces Solver::build_cost_table / build_dsi_from_table(_beta) / cost_horizontal_filter /
 // cost_vertical_filter (src/Solver.cpp:120-368), CT_pts / hamming_cost / SAD (src/cost.cpp) of the reference.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -78,6 +80,19 @@ __global__ void census_kernel(const uint8_t* __restrict__ img, uint64_t* __restr
     table[base + (size_t)y * w + x] = v;
 }
 
+// x / WIN for the small constant windows, correctly rounded like __fdiv_rn but in four instructions:
+//   q0 = RN(x * y), y = RN(1 / WIN);  r = RN(x - WIN * q0) (exact through the FMA);  q = RN(q0 + r * y).
+// tests/cpp/verify_div_const.c checks this against x / b for EVERY finite float and b in {1..5}: the only input
+// whose bits differ is x = -0 (the FMAs give +0), which the sign transfer at the end repairs.
+template <int WIN>
+__device__ __forceinline__ float div_win(float x) {
+    if constexpr (WIN == 1) return x;
+    constexpr float b = (float)WIN, y = 1.0f / (float)WIN;
+    const float q0 = __fmul_rn(x, y);
+    const float r = __fmaf_rn(-b, q0, x);
+    return copysignf(__fmaf_rn(r, y, q0), x);
+}
+
 // ---------------------------------------------------------------------------------------------
 // The reference's cost filters run IN PLACE (src/Solver.cpp:319,325 and :357,363): once the running sum
 // starts subtracting "the value WIN columns back", that column has already been overwritten with its
@@ -112,7 +127,7 @@ struct RecBox {
             const int pos = FIRST + (p - (WIN - 1));
             const int last = FIRST + (len - 2 * HALF) - 1;
             if (pos <= last) {
-                out_val = __fdiv_rn(sum, (float)WIN);
+                out_val = div_win<WIN>(sum);
                 out_pos = pos;
                 push(out_val);
                 return true;
@@ -161,6 +176,90 @@ __global__ void __launch_bounds__(128) hamming_hfilter_kernel(const uint64_t* __
             c = (float)__popcll(__ldg(rl + jl) ^ __ldg(rr + j));
         }
         if (j < RecBox<WIN>::FIRST || j > last) out[(size_t)j * d] = c;  // unfiltered border columns
+        int pos;
+        float val;
+        if (box.feed(j, c, w, pos, val)) out[(size_t)pos * d] = val;
+    }
+}
+
+// The fused Hamming + horizontal filter kernel, one block per (row, view), one thread per disparity.  The two census
+// rows are staged in shared memory once, padded by D entries of edge replication on the side the disparity shift runs
+// off (src/Solver.cpp:185 max(j - d, 0), :239 min(j + d, W - 1)), so the inner loop is two LDS.64, XOR, POPC and the
+// three-term recurrence; the steady state (columns WIN .. W-HALF-1) has no conditionals and keeps the last outputs in a
+// statically indexed circular buffer.
+template <int WIN, bool SKY>
+__global__ void __launch_bounds__(256) hamming_hfilter_row_kernel(const uint64_t* __restrict__ ct_l, const uint64_t* __restrict__ ct_r,
+                                                                   const uint8_t* __restrict__ sky_l, const uint8_t* __restrict__ sky_r,
+                                                                   float* __restrict__ cost, int h, int w, int d, int scale) {
+    using RB = RecBox<WIN>;
+    constexpr int R = RB::R;
+    extern __shared__ __align__(16) unsigned char hsm[];
+    const int i = blockIdx.x, view = blockIdx.y, k = threadIdx.x;
+    // view 0: A = left row (index j), B = right row padded on the left (index j - shift + d)
+    // view 1: A = right row (index j), B = left row padded on the right (index j + shift)
+    uint64_t* rowA = reinterpret_cast<uint64_t*>(hsm);
+    uint64_t* rowB = rowA + w;
+    uint8_t* skyrow = reinterpret_cast<uint8_t*>(rowB + w + d);
+    const uint64_t* srcA = (view == 0 ? ct_l : ct_r) + (size_t)i * w;
+    const uint64_t* srcB = (view == 0 ? ct_r : ct_l) + (size_t)i * w;
+    for (int t = k; t < w; t += blockDim.x) rowA[t] = __ldg(srcA + t);
+    for (int t = k; t < w + d; t += blockDim.x) {
+        const int src = view == 0 ? max(t - d, 0) : min(t, w - 1);
+        rowB[t] = __ldg(srcB + src);
+    }
+    if (SKY) {
+        const uint8_t* sky = view == 0 ? sky_l : sky_r;  // one of the two may be absent
+        for (int t = k; t < w; t += blockDim.x) skyrow[t] = sky ? __ldg(sky + (size_t)i * w + t) : (uint8_t)0;
+    }
+    __syncthreads();
+    const int shift = k / scale;
+    const uint64_t* pb = rowB + (view == 0 ? d - shift : shift);  // pb[j] is the partner of rowA[j]
+    float* out = cost + ((size_t)view * h + i) * (size_t)w * d + k;
+    const float sky_cost = k == 0 ? 0.0f : 999999.0f;  // src/Solver.cpp:165-179
+    auto raw = [&](int j) -> float {
+        const float c = (float)__popcll(rowA[j] ^ pb[j]);
+        if (SKY) return skyrow[j] == 255 ? sky_cost : c;
+        return c;
+    };
+
+    const int last = RB::last_filtered(w);
+    const int fast_end = last + 1;  // columns > last keep their raw value (and, for even WIN, the final step has no output)
+    RB box;
+    box.reset();
+    int j = 0;
+    // ---- lead-in: the first WIN columns through the general feed ----
+    for (; j < WIN && j < w; ++j) {
+        const float c = raw(j);
+        if (j < RB::FIRST || j > last) out[(size_t)j * d] = c;
+        int pos;
+        float val;
+        if (box.feed(j, c, w, pos, val)) out[(size_t)pos * d] = val;
+    }
+    // ---- steady state: sum += c[j]; sum -= (value WIN columns back, already filtered); out[j - back] = sum / WIN ----
+    constexpr int BACK = WIN - 1 - RB::FIRST;  // distance from the newest input to the output position
+    float circ[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) circ[r] = box.ring[r];
+    float sum = box.sum;
+    float* po = out + (size_t)(j - BACK) * d;
+    for (; j + R <= fast_end; j += R) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            sum = __fadd_rn(sum, raw(j + r));
+            sum = __fsub_rn(sum, circ[r]);
+            const float o = div_win<WIN>(sum);
+            circ[r] = o;
+            *po = o;
+            po += d;
+        }
+    }
+    // ---- tail: back to the general feed (re-aligned shift register) ----
+#pragma unroll
+    for (int r = 0; r < R; ++r) box.ring[r] = circ[r];
+    box.sum = sum;
+    for (; j < w; ++j) {
+        const float c = raw(j);
+        if (j > last) out[(size_t)j * d] = c;
         int pos;
         float val;
         if (box.feed(j, c, w, pos, val)) out[(size_t)pos * d] = val;
@@ -264,16 +363,36 @@ void launch_census(const uint8_t* img, uint64_t* table, int h, int w, int win_h,
     lc.note("census_kernel");
 }
 
+template <int WIN>
+static void launch_hh(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r, float* cost, int views,
+                      int h, int w, int d, int scale, cudaStream_t st) {
+    static const bool legacy = std::getenv("SGM_B200_HFILTER_LEGACY") != nullptr;
+    const bool sky = sky_l || sky_r;
+    const size_t smem = (size_t)(2 * w + d) * sizeof(uint64_t) + (sky ? (size_t)w : 0);
+    if (legacy || smem > 200 * 1024) {  // very wide rows: the thread-per-(row, d) form that reads the tables through L1
+        dim3 grid((h * d + 127) / 128, views);
+        hamming_hfilter_kernel<WIN><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale);
+        return;
+    }
+    dim3 grid(h, views);
+    if (sky) {
+        if (smem > 48 * 1024) cudaFuncSetAttribute(hamming_hfilter_row_kernel<WIN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        hamming_hfilter_row_kernel<WIN, true><<<grid, d, smem, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale);
+    } else {
+        if (smem > 48 * 1024) cudaFuncSetAttribute(hamming_hfilter_row_kernel<WIN, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        hamming_hfilter_row_kernel<WIN, false><<<grid, d, smem, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale);
+    }
+}
+
 void launch_hamming_hfilter(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r,
                             float* cost, int views, int h, int w, int d, int scale, int win, cudaStream_t st,
                             LaunchCounter& lc) {
-    dim3 grid((h * d + 127) / 128, views);
     switch (win) {
-        case 5: hamming_hfilter_kernel<5><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale); break;
-        case 4: hamming_hfilter_kernel<4><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale); break;
-        case 3: hamming_hfilter_kernel<3><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale); break;
-        case 2: hamming_hfilter_kernel<2><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale); break;
-        case 1: hamming_hfilter_kernel<1><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale); break;
+        case 5: launch_hh<5>(ct_l, ct_r, sky_l, sky_r, cost, views, h, w, d, scale, st); break;
+        case 4: launch_hh<4>(ct_l, ct_r, sky_l, sky_r, cost, views, h, w, d, scale, st); break;
+        case 3: launch_hh<3>(ct_l, ct_r, sky_l, sky_r, cost, views, h, w, d, scale, st); break;
+        case 2: launch_hh<2>(ct_l, ct_r, sky_l, sky_r, cost, views, h, w, d, scale, st); break;
+        case 1: launch_hh<1>(ct_l, ct_r, sky_l, sky_r, cost, views, h, w, d, scale, st); break;
         default: lc.err = cudaErrorInvalidValue; return;
     }
     lc.note("hamming_hfilter_kernel");

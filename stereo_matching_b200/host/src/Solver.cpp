@@ -1,0 +1,171 @@
+// Solver.cpp — host shell of the Solver base class over the device engine (reference: src/Solver.cpp).
+//
+// Everything the reference's Solver computes on the CPU (census tables, Hamming volume, recursive cost filters,
+// sub-pixel fit, hole-filling median, speckle filter: src/Solver.cpp:120-635) happens inside sgm_process(); this file
+// only validates, moves images in and disparities out, and draws the debug view.
+#include "../inc/Solver.h"
+
+#include <cstdio>
+#include <cstdlib>
+
+namespace {
+
+// The reference reports misuse through assert() (src/Solver.cpp:6-10, src/SGM.cpp:34-38), i.e. message + abort.
+// Engine errors are reported the same way: loudly, never by falling back to another path.
+void die(const char *what, const sgm_engine *e)
+{
+    std::fprintf(stderr, "stereo_matching_b200: %s: %s\n", what, sgm_last_error(e));
+    std::abort();
+}
+
+}  // namespace
+
+Solver::Solver(int h, int w, int s, int d)
+    : img_h(0), img_w(0), scale(s), max_disp(d), invalid_disp(d + 1), engine(nullptr)
+{
+    // same domain as the reference (src/Solver.cpp:6-10); d == 256 is the engine's widened mode (uint16 disparities
+    // inside, the CV_8UC1 `disp` Mats then saturate, get_disp() stays exact)
+    if (!(h > 0 && w > 0 && s > 0 && d > 0) || !(s == 1 || s == 2) || !(d == 32 || d == 64 || d == 128 || d == 256)) {
+        std::fprintf(stderr, "stereo_matching_b200: Solver(h=%d, w=%d, s=%d, d=%d): need h, w > 0, s in {1, 2}, d in {32, 64, 128, 256}\n", h, w, s, d);
+        std::abort();
+    }
+    img_h = h / s;
+    img_w = w / s;
+    disp.create(img_h, img_w, CV_8UC1);
+    disp_beta.create(img_h, img_w, CV_8UC1);
+    filtered_disp.create(img_h, img_w, CV_32FC1);
+    filtered_disp_beta.create(img_h, img_w, CV_32FC1);
+    colored_disp.create(img_h, img_w, CV_8UC3);
+}
+
+Solver::~Solver()
+{
+    sgm_destroy(engine);
+}
+
+void Solver::open_engine(int algo, int paths, int full_h, int full_w)
+{
+    sgm_params p;
+    sgm_default_params(&p, full_h, full_w, scale, max_disp, algo);
+    p.paths = paths;
+    p.census_h = WIN_H;
+    p.census_w = WIN_W;
+    p.box_h = COST_WIN_H;
+    p.box_w = COST_WIN_W;
+    p.unique_ratio = UNIQUE_RATIO;
+    p.lr_thresh = LR_CHECK_DIS;
+    p.median_h = MEDIAN_FILTER_H;
+    p.median_w = MEDIAN_FILTER_W;
+    p.speckle_size = SPECKLE_SIZE;
+    p.speckle_dis = SPECKLE_DIS;
+    if (const char *dev = std::getenv("SGM_B200_DEVICE")) p.device = std::atoi(dev);
+    if (sgm_create(&engine, &p) != SGM_OK) die("cannot create the device pipeline (no CPU path exists)", nullptr);
+}
+
+void Solver::run_engine(Mat &l, Mat &r)
+{
+    // src/SGM.cpp:34-38 / src/BM.cpp:11-15
+    if (l.rows != r.rows || l.cols != r.cols || l.type() != CV_8UC1 || r.type() != CV_8UC1 || l.rows / scale != img_h ||
+        l.cols / scale != img_w) {
+        std::fprintf(stderr, "stereo_matching_b200: process(): images must be CV_8UC1, equal size, %d x %d at scale %d\n",
+                     img_w * scale, img_h * scale, scale);
+        std::abort();
+    }
+    img_l = l;  // header copies: the debug view reads the left image later (src/SGM.cpp:59-60)
+    img_r = r;
+    const bool sky_l = !sky_mask.empty() && sky_mask.rows == img_h && sky_mask.cols == img_w;
+    const bool sky_r = !sky_mask_beta.empty() && sky_mask_beta.rows == img_h && sky_mask_beta.cols == img_w;
+    if (sky_l || sky_r)
+        std::printf("sky mask found\n");  // src/Solver.cpp:148
+    else
+        std::printf("no sky mask\n");     // src/Solver.cpp:151
+    if (sgm_process(engine, l.ptr<uchar>(0), l.step, r.ptr<uchar>(0), r.step, sky_l ? sky_mask.ptr<uchar>(0) : nullptr,
+                    sky_l ? (size_t)sky_mask.step : 0, sky_r ? sky_mask_beta.ptr<uchar>(0) : nullptr,
+                    sky_r ? (size_t)sky_mask_beta.step : 0) != SGM_OK)
+        die("process() failed", engine);
+
+    if (sgm_get_disparity_f32(engine, filtered_disp.ptr<float>(0), filtered_disp.step) != SGM_OK) die("get_disp", engine);
+    // the integer and right-view results the reference keeps in its protected Mats
+    std::vector<uint16_t> d16((size_t)img_h * img_w);
+    for (int view = 0; view < 2; ++view) {
+        Mat &dst = view == 0 ? disp : disp_beta;
+        if (sgm_get_disparity_u16(engine, view, d16.data(), (size_t)img_w * sizeof(uint16_t)) != SGM_OK) break;  // BM has one view
+        for (int i = 0; i < img_h; ++i) {
+            uchar *row = dst.ptr<uchar>(i);
+            for (int j = 0; j < img_w; ++j) {
+                const unsigned v = d16[(size_t)i * img_w + j];
+                row[j] = (uchar)(v > 255 ? 255 : v);
+            }
+        }
+    }
+    sky_mask.release();
+    sky_mask_beta.release();
+}
+
+void Solver::fetch_disparity(uchar *d)
+{
+    for (int i = 0; i < disp.rows; ++i) std::memcpy(disp.ptr<uchar>(i), d + (size_t)i * disp.cols, disp.cols);
+}
+
+void Solver::fetch_disparity(float *d)
+{
+    for (int i = 0; i < filtered_disp.rows; ++i)
+        std::memcpy(filtered_disp.ptr<float>(i), d + (size_t)i * filtered_disp.cols, filtered_disp.cols * sizeof(float));
+}
+
+// Piecewise-linear blue -> cyan -> green -> yellow -> red ramp over the disparity range; invalid pixels are black.
+// Same breakpoints and integer truncation as src/Solver.cpp:652-707.
+void Solver::colormap()
+{
+    const float gain = (float)(256 / max_disp);  // integer division first, as in the reference (:667)
+    for (int i = 0; i < filtered_disp.rows; ++i) {
+        const float *src = filtered_disp.ptr<float>(i);
+        Vec3b *dst = colored_disp.ptr<Vec3b>(i);
+        for (int j = 0; j < filtered_disp.cols; ++j) {
+            float v = src[j];
+            uchar b = 0, g = 0, r = 0;
+            if (!(v > max_disp - 1)) {
+                v *= gain;
+                if (v <= 51) {
+                    b = 255;
+                    g = (uchar)(v * 5);
+                } else if (v <= 102) {
+                    b = (uchar)(255 - (v - 51) * 5);
+                    g = 255;
+                } else if (v <= 153) {
+                    g = 255;
+                    r = (uchar)((v - 102) * 5);
+                } else if (v <= 204) {
+                    g = (uchar)(255 - uchar(128.0 * (v - 153) / 51.0 + 0.5));
+                    r = 255;
+                } else {
+                    g = (uchar)(127 - uchar(127.0 * (v - 204) / 51.0 + 0.5));
+                    r = 255;
+                }
+            }
+            dst[j][0] = b;
+            dst[j][1] = g;
+            dst[j][2] = r;
+        }
+    }
+}
+
+void Solver::show_disp(Mat &debug_view)
+{
+    colormap();
+    // working-resolution left image (the reference keeps the decimated copy from process(); here it is rebuilt on demand)
+    Mat gray(img_h, img_w, CV_8UC1);
+    for (int i = 0; i < img_h; ++i) {
+        const uchar *src = img_l.ptr<uchar>(scale == 1 ? i : debug_source_row(i));
+        uchar *dst = gray.ptr<uchar>(i);
+        for (int j = 0; j < img_w; ++j) dst[j] = src[j * scale];
+    }
+    Mat bgr;
+    cvtColor(gray, bgr, CV_GRAY2BGR);
+    // image on top, colour-mapped disparity below; the lower block starts at row img_h - 1 like src/Solver.cpp:91
+    debug_view = Mat::zeros(img_h * 2, img_w, CV_8UC3);
+    Mat top = debug_view(Rect(0, 0, img_w, img_h));
+    bgr.copyTo(top);
+    Mat bottom = debug_view(Rect(0, img_h - 1, img_w, img_h));
+    colored_disp.copyTo(bottom);
+}
