@@ -62,7 +62,7 @@ protected:
     Mat filtered_disp;              // CV_32FC1 final result
     Mat filtered_disp_beta;         // CV_32FC1 sub-pixel disparity of the right view (SGM only)
     Mat colored_disp;               // CV_8UC3 scratch of show_disp()
-    Mat sky_mask, sky_mask_beta;    // masks handed to the 4-argument process(); released after each frame
+    Mat sky_mask, sky_mask_beta;    // masks handed to the last 4-argument process() (kept between frames like the reference)
 
     sgm_engine *engine;             // the device pipeline (NULL until a derived constructor called open_engine)
 

@@ -98,8 +98,7 @@ void Solver::run_engine(Mat &l, Mat &r)
             }
         }
     }
-    sky_mask.release();
-    sky_mask_beta.release();
+    // the masks stay set until the next 4-argument process(), as in the reference (src/SGM.cpp:831-833)
 }
 
 void Solver::fetch_disparity(uchar *d)

@@ -1,0 +1,83 @@
+// host_shell_main.cpp — drives the C++ Solver / SGM / BM shells exactly the way the reference's node.cpp does
+// (node.cpp:49 make_shared<SGM>(h, w, scale, max_disp) into a SolverPtr; :93 process(l, r, sky, sky_beta);
+// :104 get_disp(); :107 show_disp(debug_view)) and dumps the results for tests/test_host_shell.py.
+//
+//   host_shell_main <sgm|bm> H W SCALE D in_left.raw in_right.raw [sky_l.raw sky_r.raw|- -] out_prefix
+// TEST INFRASTRUCTURE.
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "inc/BM.h"
+#include "inc/SGM.h"
+
+double get_cur_ms() {
+    using namespace std::chrono;
+    return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+static bool read_raw(const char* path, Mat& m) {
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return false;
+    bool ok = true;
+    for (int i = 0; i < m.rows && ok; ++i) ok = std::fread(m.ptr<uchar>(i), 1, m.cols, f) == (size_t)m.cols;
+    std::fclose(f);
+    return ok;
+}
+
+static void write_raw(const std::string& path, const Mat& m, size_t elem) {
+    FILE* f = std::fopen(path.c_str(), "wb");
+    for (int i = 0; i < m.rows; ++i) std::fwrite(m.ptr<uchar>(i), elem, m.cols, f);
+    std::fclose(f);
+}
+
+int main(int argc, char** argv) {
+    if (argc != 11) {
+        std::fprintf(stderr, "usage: %s <sgm|bm> H W SCALE D left.raw right.raw sky_l.raw|- sky_r.raw|- out_prefix\n", argv[0]);
+        return 2;
+    }
+    const bool bm = std::strcmp(argv[1], "bm") == 0;
+    const int h = std::atoi(argv[2]), w = std::atoi(argv[3]), s = std::atoi(argv[4]), d = std::atoi(argv[5]);
+    // a pitched left image (extra bytes per row) exercises Mat::step like a ROI of a larger image would
+    Mat big_l(h, w + 24, CV_8UC1), img_r(h, w, CV_8UC1);
+    Mat img_l = big_l(Rect(0, 0, w, h));
+    if (!read_raw(argv[6], img_l) || !read_raw(argv[7], img_r)) return 3;
+    const bool have_sky = std::strcmp(argv[8], "-") != 0;
+    Mat sky_l, sky_r;
+    if (have_sky) {
+        sky_l.create(h / s, w / s, CV_8UC1);
+        sky_r.create(h / s, w / s, CV_8UC1);
+        if (!read_raw(argv[8], sky_l) || !read_raw(argv[9], sky_r)) return 3;
+    }
+    const std::string out = argv[10];
+
+    SolverPtr sv;
+    if (bm)
+        sv = std::make_shared<BM>(h, w, s, d);
+    else
+        sv = std::make_shared<SGM>(h, w, s, d);
+    const double t0 = get_cur_ms();
+    if (have_sky)
+        sv->process(img_l, img_r, sky_l, sky_r);
+    else
+        sv->process(img_l, img_r);
+    const double t1 = get_cur_ms();
+    Mat disp = sv->get_disp();
+    Mat debug_view;
+    sv->show_disp(debug_view);
+    std::printf("time cost: %lf ms\n", t1 - t0);
+    std::printf("disp %d x %d type %d, debug view %d x %d channels %d\n", disp.rows, disp.cols, disp.type(), debug_view.rows,
+                debug_view.cols, debug_view.channels());
+    write_raw(out + "_disp.f32", disp, sizeof(float));
+    write_raw(out + "_debug.bgr", debug_view, 3);
+    // second frame on the same solver (node.cpp would loop over frames): must give the same result
+    if (have_sky)
+        sv->process(img_l, img_r, sky_l, sky_r);
+    else
+        sv->process(img_l, img_r);
+    write_raw(out + "_disp2.f32", sv->get_disp(), sizeof(float));
+    return 0;
+}
