@@ -13,8 +13,9 @@ of the device-timed region.  Prints ONE JSON line on rank 0.
   value     frames/s, whole job, inputs already resident in HBM (sgm_enqueue_device), results left on device
   e2e       frames/s through the reference-facing C ABI with HOST buffers (sgm_enqueue / sgm_wait:
             pinned staging + H2D + kernels + D2H inside the timed region)
-  roofline  aggregation stage (all path kernels incl. fused WTA epilogue): algorithmic 96*W*H*D bytes per frame
-             / its CUDA-event duration on the engine's stream, vs the measured HBM copy peak
+  roofline  aggregation stage (horizontal pair kernel + down sweep + up sweep incl. the fused WTA epilogue): algorithmic
+            96*W*H*D bytes per frame / its CUDA-event duration on the engine's stream, vs the measured
+            HBM copy peak; `traffic` = DRAM bytes of those kernels from the committed ncu capture
   cpu_baseline  the reference's own CPU sources (oracle/_ref) on this box's host cores, bounded sample
 
 --impl reference times the reference CPU implementation only (rank 0), same metric / unit / config.
@@ -366,7 +367,7 @@ def main():
             "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": 2 * H * W * FRAMES_PER_STEP,
                     "d2h_bytes_per_step": 4 * H * W * FRAMES_PER_STEP, "gdisp_px_per_s": fps_e2e * n_px / 1e9},
             "gpu_launches": r["launches"],
-            "roofline": {"kernel": "aggregation stage: 8 sgm_path_kernel launches per frame (both views per launch), last one fused with sum/WTA/uniqueness/sub-pixel",
+            "roofline": {"kernel": "aggregation stage = sgm_hpair_async_kernel + sgm_sweep_kernel<DOWN> + sgm_sweep_kernel<UP> (3 launches per frame, both views per launch; the up sweep ends in the fused sum/WTA/uniqueness/sub-pixel epilogue)",
                          "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": load_traffic(), "peak_source": peak_src, "algorithmic_bytes_per_frame": alg_bytes,
                          "ms_per_frame": agg_ms, "timing": "engine-side CUDA events on the launching stream, frames run serially"},
