@@ -116,7 +116,12 @@ def cpu_reference_time(pairs, steps, warmup):
 
     times = []
     if refbind.available():
-        kind, cores = "reference", refbind.max_threads()
+        # all host threads this process may use: torchrun exports OMP_NUM_THREADS=1, which must not throttle the baseline
+        try:
+            cores = len(os.sched_getaffinity(0))
+        except AttributeError:
+            cores = os.cpu_count() or 1
+        kind = "reference"
         refbind.set_threads(cores)
         # one Solver instance reused for all frames, as node.cpp does (src/Solver.cpp allocates ~2.1 GB in the ctor)
         L, R = pairs[0]

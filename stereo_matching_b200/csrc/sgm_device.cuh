@@ -50,6 +50,58 @@ __device__ __forceinline__ void path_step(float (&L)[LaneLayout<D>::E], const fl
     m = warp_min_f32(lm);
 }
 
+// N independent paths of the SAME pixel advanced together (they share C but not their predecessors): the shuffles of all
+// N are issued first, then the arithmetic, then the N warp minima, so the fixed latencies of one path's chain
+// (SHFL -> FMNMX -> FADD -> FMNMX3 -> FADD -> CREDUX) are covered by the other paths' instructions.  Same operations
+// and rounding as path_step, per path.
+template <int D, int N>
+__device__ __forceinline__ void path_step_n(float (&L)[N][LaneLayout<D>::E], const float (&C)[LaneLayout<D>::E], float (&m)[N],
+                                            int lane, float P1, float P2) {
+    using LL = LaneLayout<D>;
+    constexpr int E = LL::E, CW = LL::CW, NCH = LL::NCH;
+    float up[N][NCH], dn[N][NCH];
+#pragma unroll
+    for (int n = 0; n < N; ++n)
+#pragma unroll
+        for (int q = 0; q < NCH; ++q) {
+            up[n][q] = __shfl_sync(FULL_MASK, L[n][q * CW + CW - 1], (lane + 31) & 31);
+            dn[n][q] = __shfl_sync(FULL_MASK, L[n][q * CW], (lane + 1) & 31);
+        }
+    float lm[N];
+#pragma unroll
+    for (int n = 0; n < N; ++n) {
+        const float mP2 = __fadd_rn(m[n], P2);
+        float nL[E];
+#pragma unroll
+        for (int q = 0; q < NCH; ++q) {
+#pragma unroll
+            for (int e = 0; e < CW; ++e) {
+                const int k = q * CW + e;
+                float lo, hi;
+                if (e > 0)
+                    lo = L[n][k - 1];
+                else
+                    lo = lane > 0 ? up[n][q] : (q > 0 ? up[n][q > 0 ? q - 1 : 0] : L[n][k]);
+                if (e < CW - 1)
+                    hi = L[n][k + 1];
+                else
+                    hi = lane < 31 ? dn[n][q] : (q < NCH - 1 ? dn[n][q < NCH - 1 ? q + 1 : q] : L[n][k]);
+                const float nb = __fadd_rn(fminf(lo, hi), P1);
+                const float t = min3f(nb, L[n][k], mP2);
+                nL[k] = __fadd_rn(t, __fsub_rn(C[k], m[n]));
+            }
+        }
+        lm[n] = nL[0];
+#pragma unroll
+        for (int k = 0; k < E; ++k) {
+            L[n][k] = nL[k];
+            lm[n] = fminf(lm[n], nL[k]);
+        }
+    }
+#pragma unroll
+    for (int n = 0; n < N; ++n) m[n] = warp_min_f32(lm[n]);
+}
+
 // WTA + uniqueness + sub-pixel on one pixel's summed costs held across the warp.
 //   src/SGM.cpp:381-416 / src/BM.cpp:59-89: first strict minimum; first occurrence of the smallest value
 //   different from it; invalid (D+1) iff min/sec > ratio && |min_d - sec_d| > min_gap.

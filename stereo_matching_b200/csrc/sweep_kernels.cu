@@ -422,52 +422,108 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                 asm volatile("cp.async.wait_group %0;" ::"n"(PF - 1) : "memory");  // this row's C / A / B have landed
                 lds_pixel<D>(rbase + u * SLOT_BYTES, C);
                 if (DIAG && r > 0 && !(a.debug & 2)) mbar_wait(bar, par ^ 1u);  // every warp's row r-1 vectors are in shared memory
-                // ---- F: first diagonal ----
-                if (DIAG) {
-                    float mF;
-                    if (r == 0 || f_init) {
-#pragma unroll
-                        for (int k = 0; k < E; ++k) F[k] = C[k];
-                        mF = warp_min_f32(vec_min<E>(F));
-                    } else {
-                        lds_pixel<D>(f_src + (par ^ 1u) * PAR_BYTES, F);
-                        mF = lds_f32(fm_src + (par ^ 1u) * MIN_PAR_BYTES);
-                        path_step<D>(F, C, mF, lane, a.P1, a.P2);
-                    }
-                    if (f_pub) HIO::publish(f_pub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, F, tag);
-                    sts_pixel<D>(f_dst + par * PAR_BYTES, F);
-                    if (lane == 0) sts_f32(fm_dst + par * MIN_PAR_BYTES, mF);
-                }
-                // ---- V: vertical path ----
+                // ---- the three recurrences of this pixel (P[0] = F, P[1] = V, P[2] = G) ----
+                // F, V and G only depend on the previous row, not on each other, so they advance together
+                // (path_step_n) unless G has to wait for a neighbouring block: then F goes first and is published,
+                // and V and G follow together.
                 if (r == 0) {
 #pragma unroll
-                    for (int k = 0; k < E; ++k) V[k] = C[k];
+                    for (int k = 0; k < E; ++k) F[k] = V[k] = G[k] = C[k];
                     mV = warp_min_f32(vec_min<E>(V));
-                } else {
-                    path_step<D>(V, C, mV, lane, a.P1, a.P2);
-                }
-                // ---- G: second diagonal ----
-                if (DIAG) {
-                    float mG;
-                    if (r == 0 || g_init) {
-#pragma unroll
-                        for (int k = 0; k < E; ++k) G[k] = C[k];
-                        mG = warp_min_f32(vec_min<E>(G));
-                    } else {
-                        if (g_global) {
-                            if (!dead && !(a.debug & 1) && !HIO::consume(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, G, tag - 1u)) {
-                                dead = true;
-                                if (lane == 0) atomicExch(a.error, 1);
-                            }
-                            mG = warp_min_f32(vec_min<E>(G));
-                        } else {
-                            lds_pixel<D>(g_src + (par ^ 1u) * PAR_BYTES, G);
-                            mG = lds_f32(gm_src + (par ^ 1u) * MIN_PAR_BYTES);
+                    if (DIAG) {
+                        if (f_pub) HIO::publish(f_pub, lane, F, tag);
+                        sts_pixel<D>(f_dst + par * PAR_BYTES, F);
+                        sts_pixel<D>(g_dst + par * PAR_BYTES, G);
+                        if (lane == 0) {
+                            sts_f32(fm_dst + par * MIN_PAR_BYTES, mV);
+                            sts_f32(gm_dst + par * MIN_PAR_BYTES, mV);
                         }
-                        path_step<D>(G, C, mG, lane, a.P1, a.P2);
                     }
+                } else if (!DIAG) {
+                    path_step<D>(V, C, mV, lane, a.P1, a.P2);
+                } else {
+                    float P[3][E], mP[3];
+                    // previous-row vectors: F and (unless it comes from another block) G from shared memory
+                    if (!f_init) {
+                        lds_pixel<D>(f_src + (par ^ 1u) * PAR_BYTES, P[0]);
+                        mP[0] = lds_f32(fm_src + (par ^ 1u) * MIN_PAR_BYTES);
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < E; ++k) P[0][k] = C[k];  // placeholder, overwritten below
+                        mP[0] = 0.f;
+                    }
+#pragma unroll
+                    for (int k = 0; k < E; ++k) P[1][k] = V[k];
+                    mP[1] = mV;
+                    if (!g_global) {
+                        if (!g_init) {
+                            lds_pixel<D>(g_src + (par ^ 1u) * PAR_BYTES, P[2]);
+                            mP[2] = lds_f32(gm_src + (par ^ 1u) * MIN_PAR_BYTES);
+                        } else {
+#pragma unroll
+                            for (int k = 0; k < E; ++k) P[2][k] = C[k];
+                            mP[2] = 0.f;
+                        }
+                        path_step_n<D, 3>(P, C, mP, lane, a.P1, a.P2);
+                    } else {
+                        // block-edge warp: F first (a neighbouring block is waiting for it), then V and G together
+                        float P0[1][E], m0[1] = {mP[0]};
+#pragma unroll
+                        for (int k = 0; k < E; ++k) P0[0][k] = P[0][k];
+                        path_step_n<D, 1>(P0, C, m0, lane, a.P1, a.P2);
+                        if (f_init) {
+#pragma unroll
+                            for (int k = 0; k < E; ++k) P0[0][k] = C[k];
+                            m0[0] = warp_min_f32(vec_min<E>(C));
+                        }
+                        if (f_pub) HIO::publish(f_pub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, P0[0], tag);
+                        float P12[2][E], m12[2];
+                        if (!dead && !(a.debug & 1) && !HIO::consume(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, P12[1], tag - 1u)) {
+                            dead = true;
+                            if (lane == 0) atomicExch(a.error, 1);
+                        }
+#pragma unroll
+                        for (int k = 0; k < E; ++k) P12[0][k] = V[k];
+                        m12[0] = mV;
+                        m12[1] = warp_min_f32(vec_min<E>(P12[1]));
+                        path_step_n<D, 2>(P12, C, m12, lane, a.P1, a.P2);
+#pragma unroll
+                        for (int k = 0; k < E; ++k) {
+                            P[0][k] = P0[0][k];
+                            P[1][k] = P12[0][k];
+                            P[2][k] = P12[1][k];
+                        }
+                        mP[0] = m0[0];
+                        mP[1] = m12[0];
+                        mP[2] = m12[1];
+                    }
+                    if (!g_global) {  // image-border columns restart their diagonal on every row (src/SGM.cpp:266,282,330,346)
+                        if (f_init) {
+#pragma unroll
+                            for (int k = 0; k < E; ++k) P[0][k] = C[k];
+                            mP[0] = warp_min_f32(vec_min<E>(C));
+                        }
+                        if (g_init) {
+#pragma unroll
+                            for (int k = 0; k < E; ++k) P[2][k] = C[k];
+                            mP[2] = warp_min_f32(vec_min<E>(C));
+                        }
+                    }  // (f_pub != nullptr implies g_global, handled above)
+#pragma unroll
+                    for (int k = 0; k < E; ++k) {
+                        F[k] = P[0][k];
+                        V[k] = P[1][k];
+                        G[k] = P[2][k];
+                    }
+                    mV = mP[1];
+                    sts_pixel<D>(f_dst + par * PAR_BYTES, F);
                     sts_pixel<D>(g_dst + par * PAR_BYTES, G);
-                    if (lane == 0) sts_f32(gm_dst + par * MIN_PAR_BYTES, mG);
+                    if (lane == 0) {
+                        sts_f32(fm_dst + par * MIN_PAR_BYTES, mP[0]);
+                        sts_f32(gm_dst + par * MIN_PAR_BYTES, mP[2]);
+                    }
+                }
+                if (DIAG) {
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar);  // this warp's row r vectors are published
                 }
