@@ -2,6 +2,8 @@
 //
 // Replaces src/SGM.cpp:803-818 and Solver::post_filter (src/Solver.cpp:600-635, speckle_filter_new
 // :514-566) of the reference, with the reference's serial (single-thread) semantics.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -155,6 +157,81 @@ __global__ void __launch_bounds__(1024) median_fill_ring_kernel(const float* __r
     }
 }
 
+// Batched form of the ring wavefront.  With a skew of K columns per row, a row may advance B = K - RW consecutive columns
+// between two barriers: a hole at (i, c + b), b < B, needs row i-1 final up to column c + b + RW <= c + K - 1, which row
+// i-1 (cursor c + K) finished in earlier batches, and rows below have not touched what it reads (their cursors trail by
+// K, 2K, ...).  Same raster-order result with (W + K*H) / B barriers instead of W + 3*H.
+template <int WH, int WW, int K, int RING, int LEADB>
+__global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __restrict__ src, float* __restrict__ f, int h, int w,
+                                                                  int d) {
+    constexpr int RH = WH / 2, RW = WW / 2, B = K - RW, NWIN = WH * WW, LOOK = K * RH + RW, AHEAD = LOOK + 1;
+    static_assert(B >= 1 && AHEAD + LEADB * B + B + LOOK < RING && (RING & (RING - 1)) == 0, "window does not fit the ring");
+    extern __shared__ float ring[];  // [h][RING]
+    const float vmax = (float)(d - 1);
+    const int i = threadIdx.x;       // one row per thread (h <= blockDim.x)
+    const bool row_ok = i < h;
+    const bool interior_row = i >= RH && i < h - RH;
+    float* myring = ring + (size_t)(row_ok ? i : 0) * RING;
+    const float* mysrc = src + (size_t)(row_ok ? i : 0) * w;
+    // batch n: row i's cursor is c = n*B - K*i.  First batch: the top row needs its first AHEAD + LEADB*B columns requested.
+    const int n_first = -((AHEAD + LEADB * B + B - 1) / B);
+    const int n_last = ((w - 1) + K * (h - 1)) / B;
+    for (int n = n_first; n <= n_last; ++n) {
+        const int c = n * B - K * i;
+        if (row_ok) {
+            const int cf = c + AHEAD + LEADB * B;
+#pragma unroll
+            for (int b = 0; b < B; ++b) {
+                const int x = cf + b;
+                if (x >= 0 && x < w) {
+                    const unsigned dst = (unsigned)__cvta_generic_to_shared(myring + (x & (RING - 1)));
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(mysrc + x));
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;");
+        asm volatile("cp.async.wait_group %0;" ::"n"(LEADB));
+        __syncthreads();  // feeds of batch n - LEADB and the fills of batch n - 1 are visible
+        if (interior_row) {
+#pragma unroll 1
+            for (int b = 0; b < B; ++b) {
+                const int x = c + b;
+                if (x < RW || x >= w - RW) continue;
+                const float own = myring[x & (RING - 1)];
+                if (own <= vmax) continue;  // not a hole
+                int vals[NWIN];
+                int cnt = 0;
+#pragma unroll
+                for (int a = -RH; a <= RH; ++a)
+#pragma unroll
+                    for (int e = -RW; e <= RW; ++e) {
+                        const float v = ring[(size_t)(i + a) * RING + ((x + e) & (RING - 1))];
+                        const bool ok = v <= vmax;
+                        vals[(a + RH) * WW + (e + RW)] = ok ? (int)v : 0x7fffffff;  // float -> int truncation (:619)
+                        cnt += ok ? 1 : 0;
+                    }
+                if (cnt > NWIN / 2) {
+                    const int need = cnt / 2 + 1;  // sorted[cnt / 2] = smallest v with #(vals <= v) >= cnt/2 + 1
+                    int lo = 0, hi = d - 1;
+                    while (lo < hi) {
+                        const int mid = (lo + hi) >> 1;
+                        int le = 0;
+#pragma unroll
+                        for (int q = 0; q < NWIN; ++q) le += vals[q] <= mid ? 1 : 0;
+                        if (le >= need)
+                            hi = mid;
+                        else
+                            lo = mid + 1;
+                    }
+                    const float fill = (float)lo;
+                    f[(size_t)i * w + x] = fill;
+                    myring[x & (RING - 1)] = fill;  // later pixels of this row in this batch, and everyone after the barrier
+                }
+            }
+        }
+    }
+}
+
 // ---- speckle filter: exact 4-connected components under |a - b| < max_dis (src/Solver.cpp:514-566) -----
 // Union-find with min-index roots.  Labels only ever decrease and always stay inside the component, so a
 // stale read merely costs extra hops.
@@ -260,7 +337,13 @@ void launch_median_fill(const float* src, float* f, int h, int w, int d, int win
     int threads = ((h + 31) / 32) * 32;
     if (threads > 1024) threads = 1024;
     const size_t ring_bytes = (size_t)h * 32 * sizeof(float);
-    if (win_h == 5 && win_w == 5 && ring_bytes <= 200 * 1024 && h <= 2048 && d <= 65536) {
+    static const bool legacy = std::getenv("SGM_B200_MEDIAN_LEGACY") != nullptr;
+    if (!legacy && win_h == 5 && win_w == 5 && h <= 1024 && (size_t)h * 64 * sizeof(float) <= 200 * 1024) {
+        // batched wavefront: skew 6, 4 columns per barrier, 64-column rings
+        const size_t bytes = (size_t)h * 64 * sizeof(float);
+        cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        median_fill_batch_kernel<5, 5, 6, 64, 3><<<1, threads, bytes, st>>>(src, f, h, w, d);
+    } else if (win_h == 5 && win_w == 5 && ring_bytes <= 200 * 1024 && h <= 2048 && d <= 65536) {
         // shared-memory ring form (the common case); the L2 form below stays as the fallback for very tall images
         if (h <= 1024) {
             cudaFuncSetAttribute(median_fill_ring_kernel<5, 5, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes);
