@@ -316,6 +316,25 @@ def run_gpu_arm(args, rank, world, local, dist):
                 inflight=inflight, device_bytes=engines[0].device_bytes)
 
 
+def gpu_sgm_reference_time():
+    """The reference's own CUDA class GPU_SGM (gpu_sgm/, compiled unmodified into oracle/_ref/libgpu_sgm_ref.so) timed on
+    this GPU in a separate process: a reported baseline only (approximate algorithm, left view only, not bit-comparable)."""
+    lib = os.path.join(ROOT, "oracle", "_ref", "libgpu_sgm_ref.so")
+    if not os.path.exists(lib):
+        return {"unavailable": "oracle/_ref/libgpu_sgm_ref.so not built"}
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "run_gpu_sgm_ref.py"), str(H), str(W), str(D), "5"],
+                           capture_output=True, text=True, timeout=120)
+        last = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+        if r.returncode != 0 or not last:
+            return {"unavailable": f"run failed (rc {r.returncode})"}
+        j = json.loads(last[-1])
+        return {"value": j["frames_per_s_steady"], "unit": "frames/s", "ms_per_frame": j["ms_per_frame"], "kind": "reference gpu_sgm",
+                "note": "GPU_SGM::process: approximate algorithm, left view only, no LR check; same 1242x375 D=128 pair"}
+    except Exception as e:  # a baseline must never take the bench down
+        return {"unavailable": f"{type(e).__name__}: {e}"}
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -387,6 +406,8 @@ def main():
                                     "sample": f"{len(times)} frames of the same 1242x375 D=128 workload after 1 warm-up, SGM::process (src/SGM.cpp:32-826), OpenMP on all host threads"}
         else:
             line["cpu_baseline"] = None
+        if not args.no_cpu_baseline and world == 1:
+            line["gpu_sgm_reference"] = gpu_sgm_reference_time()
         print(json.dumps(line), flush=True)
     if dist is not None:
         dist.barrier()
