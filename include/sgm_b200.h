@@ -150,6 +150,23 @@ SGM_API size_t sgm_device_bytes(const sgm_engine* e);
 SGM_API int sgm_cost_volume_sad(int device, const uint8_t* left, const uint8_t* right, int height, int width, int max_disp,
                         int win_h, int win_w, int scale, float* out);
 
+/* Solver::show_disp(debug_view) (src/Solver.cpp:55-93) with Solver::colormap (:652-707), rendered on the device from the
+ * last frame: dst is a (2 * height/scale) x (width/scale) 8-bit BGR image (3 bytes per pixel, dst_stride bytes per row):
+ * the working-resolution left image on top, the colour-mapped disparity from row height/scale - 1 on. */
+SGM_API int sgm_render_debug_view(sgm_engine* e, uint8_t* dst_bgr, size_t dst_stride);
+
+/* The disparity -> point cloud loop of node.cpp:119-143 on the device, for the last frame: every pixel, in raster order,
+ * whose disparity is valid and whose depth Zc = (fx+fy)/2 * baseline / (d + 1e-6) is <= max_range yields
+ * (Xc, Yc, Zc) = ((j*scale - cx) * Zc / fx, (i*scale - cy) * Zc / fy, Zc) and the grey value left(i, j).
+ * xyz receives 3 doubles per point, intensity 1 byte per point (either may be NULL), at most `capacity` points;
+ * *count receives the number of points found (it can exceed capacity: call again with larger buffers). */
+typedef struct sgm_camera {
+    float fx, fy, cx, cy;   /* CamIntrinsics of inc/utils.h:14-20 */
+    double baseline;        /* node.cpp:118 (0.5) */
+    float max_range;        /* node.cpp:117 (100) */
+} sgm_camera;
+SGM_API int sgm_point_cloud(sgm_engine* e, const sgm_camera* cam, double* xyz, uint8_t* intensity, size_t capacity, size_t* count);
+
 SGM_API int sgm_abi_version(void);
 
 #ifdef __cplusplus

@@ -177,6 +177,35 @@ double ref_process(int algo, int h, int w, int scale, int d, const uint8_t* left
     return ms;
 }
 
+// Solver::show_disp after one process(): debug_view_out is (2*h/scale) x (w/scale) x 3 BGR (pins oracle/restate.py's
+// colormap / debug_view and the device rendering).  Returns 0, or -1 on bad arguments.
+int ref_show_disp(int algo, int h, int w, int scale, int d, const uint8_t* left, const uint8_t* right, uint8_t* debug_view_out,
+                  float* fdisp) {
+    if (!left || !right || !debug_view_out || h <= 0 || w <= 0) return -1;
+    StdoutMute mute;
+    cv::Mat L(h, w, CV_8UC1), R(h, w, CV_8UC1);
+    std::memcpy(L.data, left, (size_t)h * w);
+    std::memcpy(R.data, right, (size_t)h * w);
+    const int ih = h / scale, iw = w / scale;
+    auto run = [&](auto& sv) {
+        sv.process(L, R);
+        cv::Mat view;
+        sv.show_disp(view);
+        for (int i = 0; i < 2 * ih; ++i) std::memcpy(debug_view_out + (size_t)i * iw * 3, view.template ptr<uint8_t>(i), (size_t)iw * 3);
+        if (fdisp) copy_mat_f32(sv.get_disp(), fdisp);
+    };
+    if (algo == 0) {
+        Probe<SGM> sv(h, w, scale, d);
+        run(sv);
+    } else if (algo == 1) {
+        Probe<BM> sv(h, w, scale, d);
+        run(sv);
+    } else {
+        return -1;
+    }
+    return 0;
+}
+
 // Times `iters` back-to-back process() calls on one Solver instance (as node.cpp would reuse it);
 // ms_out[k] = wall time of call k.  Used by bench.py's cpu_baseline / --impl reference legs.
 int ref_time_process(int algo, int h, int w, int scale, int d, const uint8_t* left, const uint8_t* right, int iters,

@@ -39,6 +39,9 @@ def lib():
         L.ref_hamming_cost.argtypes = [C.c_uint64, C.c_uint64]
         L.ref_gaussian_blur.restype = C.c_int
         L.ref_gaussian_blur.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_double]
+        if hasattr(L, "ref_show_disp"):
+            L.ref_show_disp.restype = C.c_int
+            L.ref_show_disp.argtypes = [C.c_int] * 5 + [C.c_void_p] * 4
         L.ref_set_threads.argtypes = [C.c_int]
         L.ref_set_quiet.argtypes = [C.c_int]
         L.ref_max_threads.restype = C.c_int
@@ -86,6 +89,18 @@ def process(algo, left, right, scale, d, sky_l=None, sky_r=None, want_cost=False
     if want_cost:
         out["cost_last"] = cost
     return out
+
+
+def show_disp(algo, left, right, scale, d):
+    """process() then Solver::show_disp: (debug view uint8 [2*ih, iw, 3], final float disparity)."""
+    left, right = _u8(left), _u8(right)
+    h, w = left.shape
+    ih, iw = h // scale, w // scale
+    view = np.zeros((2 * ih, iw, 3), np.uint8)
+    f = np.zeros((ih, iw), np.float32)
+    if lib().ref_show_disp(ALGO[algo], h, w, scale, d, _p(left), _p(right), _p(view), _p(f)) != 0:
+        raise RuntimeError("ref_show_disp failed")
+    return view, f
 
 
 def time_process(algo, left, right, scale, d, iters):

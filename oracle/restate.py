@@ -111,3 +111,63 @@ def process(left, right, scale, d, algo="sgm", sky_l=None, sky_r=None, taps=LIGH
 def fnv1a64(buf) -> str:
     a = np.ascontiguousarray(buf)
     return f"{lib().orc_fnv1a64(a.ctypes.data, a.nbytes):016x}"
+
+
+# ---------------------------------------------------------------------------------------------
+# Consumers of the final disparity (numpy restatements; TEST INFRASTRUCTURE like the rest of oracle/)
+def colormap(f, d) -> np.ndarray:
+    """Solver::colormap (src/Solver.cpp:652-707): float32 disparity -> (h, w, 3) BGR, with the reference's float / double
+    arithmetic and float -> uchar truncations.  Pinned against the compiled reference's show_disp in tests/test_oracle_cpu.py."""
+    f = np.asarray(f, np.float32)
+    out = np.zeros(f.shape + (3,), np.uint8)
+    v = f * np.float32(256 // d)
+    valid = ~(f > np.float32(d - 1))
+    s1 = valid & (v <= 51)
+    s2 = valid & ~s1 & (v <= 102)
+    s3 = valid & ~s1 & ~s2 & (v <= 153)
+    s4 = valid & ~s1 & ~s2 & ~s3 & (v <= 204)
+    s5 = valid & ~s1 & ~s2 & ~s3 & ~s4
+    five = np.float32(5)
+    out[s1, 0] = 255
+    out[s1, 1] = (v[s1] * five).astype(np.int32).astype(np.uint8)
+    t = v[s2] - np.float32(51)
+    out[s2, 0] = (np.float32(255) - t * five).astype(np.int32).astype(np.uint8)
+    out[s2, 1] = 255
+    t = v[s3] - np.float32(102)
+    out[s3, 1] = 255
+    out[s3, 2] = (t * five).astype(np.int32).astype(np.uint8)
+    t = (v[s4] - np.float32(153)).astype(np.float64)
+    out[s4, 1] = (255 - (128.0 * t / 51.0 + 0.5).astype(np.int32).astype(np.uint8).astype(np.int32)).astype(np.uint8)
+    out[s4, 2] = 255
+    t = (v[s5] - np.float32(204)).astype(np.float64)
+    out[s5, 1] = (127 - (127.0 * t / 51.0 + 0.5).astype(np.int32).astype(np.uint8).astype(np.int32)).astype(np.uint8)
+    out[s5, 2] = 255
+    return out
+
+
+def debug_view(left, f, d, scale=1, bm_rows=False) -> np.ndarray:
+    """Solver::show_disp (src/Solver.cpp:55-93): working-resolution left image as BGR on top, colour map copied over
+    rows h-1 .. 2h-2, last row zero.  bm_rows: BM decimates with source row i instead of i*scale (src/BM.cpp:23-24)."""
+    ih, iw = f.shape
+    gray = np.asarray(left)[:: (1 if (bm_rows or scale == 1) else scale)][:ih, ::scale][:, :iw]
+    out = np.zeros((2 * ih, iw, 3), np.uint8)
+    out[:ih] = gray[:, :, None]
+    out[ih - 1: 2 * ih - 1] = colormap(f, d)
+    return out
+
+
+def point_cloud(f, left, d, scale, fx, fy, cx, cy, baseline=0.5, max_range=100.0):
+    """node.cpp:119-143: raster-order list of camera-frame points and grey values.  (fx + fy) is a float add, the rest of
+    Zc is double; (j*scale - cx) is a float subtraction; the grey value is left(i, j) with WORKING-resolution indices."""
+    f = np.asarray(f, np.float32)
+    ih, iw = f.shape
+    fx, fy, cx, cy = (np.float32(x) for x in (fx, fy, cx, cy))
+    jj, ii = np.meshgrid(np.arange(iw, dtype=np.int32), np.arange(ih, dtype=np.int32))
+    with np.errstate(divide="ignore"):
+        Z = np.float64(fx + fy) / 2.0 * np.float64(baseline) / (f.astype(np.float64) + 1e-6)
+    keep = (f != np.float32(d + 1)) & ~(Z > np.float64(np.float32(max_range)))
+    X = ((jj * scale).astype(np.float32) - cx).astype(np.float64) * Z / np.float64(fx)
+    Y = ((ii * scale).astype(np.float32) - cy).astype(np.float64) * Z / np.float64(fy)
+    xyz = np.stack([X[keep], Y[keep], Z[keep]], axis=1)
+    inten = np.asarray(left)[:ih, :iw][keep]
+    return xyz, inten

@@ -14,7 +14,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsgm_b200.so")
-SOURCES = ["engine.cu", "cost_kernels.cu", "aggregate_kernels.cu", "sweep_kernels.cu", "post_kernels.cu"]
+SOURCES = ["engine.cu", "cost_kernels.cu", "aggregate_kernels.cu", "sweep_kernels.cu", "post_kernels.cu", "view_kernels.cu"]
 HEADERS = ["common.cuh", "kernels.h", "sgm_device.cuh", os.path.join("..", "..", "include", "sgm_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false", "--cudart", "static",

@@ -24,7 +24,7 @@ EXPORTS = [
     "sgm_abi_version", "sgm_default_params", "sgm_create", "sgm_destroy", "sgm_last_error", "sgm_process", "sgm_enqueue",
     "sgm_wait", "sgm_enqueue_device", "sgm_get_disparity_f32", "sgm_get_disparity_u8", "sgm_get_disparity_u16",
     "sgm_disparity_device", "sgm_tap_bytes", "sgm_get_tap", "sgm_get_size", "sgm_get_launch_count", "sgm_get_stage_ms",
-    "sgm_get_stream", "sgm_device_bytes", "sgm_cost_volume_sad",
+    "sgm_get_stream", "sgm_device_bytes", "sgm_cost_volume_sad", "sgm_render_debug_view", "sgm_point_cloud",
 ]
 
 
@@ -33,6 +33,12 @@ class Params(C.Structure):
                                           "census_w", "box_w", "box_h")] + [("unique_ratio", C.c_float), ("lr_thresh", C.c_float)] +
                 [(k, C.c_int32) for k in ("median_h", "median_w", "speckle_size", "speckle_dis", "sad_h", "sad_w", "device")] +
                 [("flags", C.c_uint32)])
+
+
+class Camera(C.Structure):
+    """sgm_camera: CamIntrinsics (inc/utils.h:14-20) + baseline / max_range of node.cpp:117-118."""
+    _fields_ = [("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float), ("baseline", C.c_double),
+                ("max_range", C.c_float)]
 
 
 class SgmError(RuntimeError):
@@ -79,6 +85,8 @@ def lib():
         L.sgm_device_bytes.argtypes = [vp]
         L.sgm_device_bytes.restype = sz
         L.sgm_cost_volume_sad.argtypes = [i, vp, vp, i, i, i, i, i, i, vp]
+        L.sgm_render_debug_view.argtypes = [vp, vp, sz]
+        L.sgm_point_cloud.argtypes = [vp, C.POINTER(Camera), C.POINTER(C.c_double), vp, sz, C.POINTER(sz)]
         _lib = L
     return _lib
 
@@ -190,6 +198,22 @@ class Solver:
         out = np.empty(shape, dt)
         self._check(lib().sgm_get_tap(self._h, TAP[name], view, out.ctypes.data, out.nbytes))
         return out
+
+    def debug_view(self) -> np.ndarray:
+        """Solver::show_disp(debug_view) (src/Solver.cpp:55-93): (2*img_h, img_w, 3) BGR."""
+        out = np.empty((2 * self.img_h, self.img_w, 3), np.uint8)
+        self._check(lib().sgm_render_debug_view(self._h, out.ctypes.data, out.strides[0]))
+        return out
+
+    def point_cloud(self, fx, fy, cx, cy, baseline=0.5, max_range=100.0):
+        """node.cpp:119-143: (xyz float64 [n, 3], intensity uint8 [n]) in raster order."""
+        cam = Camera(fx, fy, cx, cy, baseline, max_range)
+        cap = self.img_h * self.img_w
+        xyz = np.empty((cap, 3), np.float64)
+        inten = np.empty(cap, np.uint8)
+        n = C.c_size_t()
+        self._check(lib().sgm_point_cloud(self._h, C.byref(cam), xyz.ctypes.data_as(C.POINTER(C.c_double)), inten.ctypes.data, cap, C.byref(n)))
+        return xyz[: n.value].copy(), inten[: n.value].copy()
 
     @property
     def launches(self) -> int:

@@ -50,6 +50,14 @@ struct sgm_engine {
     int* d_error = nullptr;                  // fused aggregation: time-out flag
     int* h_error = nullptr;                  // pinned copy of d_error
     bool fused = false;                      // last frame used the fused schedule
+    // consumers of the result (allocated on first use)
+    uint8_t* d_view = nullptr;               // [2*ih][iw][3] debug view
+    int* d_pc_counts = nullptr;              // point cloud: per-block counts / offsets
+    int* d_pc_offsets = nullptr;
+    double* d_pc_xyz = nullptr;              // [n][3]
+    uint8_t* d_pc_int = nullptr;             // [n]
+    const uint8_t* last_left = nullptr;      // device pointer / stride of the last frame's full-resolution left image
+    size_t last_left_stride = 0;
     // pinned host
     uint8_t* h_in[2] = {nullptr, nullptr};
     uint8_t* h_sky[2] = {nullptr, nullptr};
@@ -112,6 +120,11 @@ void release(sgm_engine* e) {
     cudaFree(e->d_area);
     cudaFree(e->d_halo);
     cudaFree(e->d_error);
+    cudaFree(e->d_view);
+    cudaFree(e->d_pc_counts);
+    cudaFree(e->d_pc_offsets);
+    cudaFree(e->d_pc_xyz);
+    cudaFree(e->d_pc_int);
     cudaFreeHost(e->h_error);
     cudaFreeHost(e->h_final);
     for (auto& ev : e->ev)
@@ -367,6 +380,8 @@ int sgm_enqueue(sgm_engine* e, const uint8_t* left, size_t ls, const uint8_t* ri
     LaunchCounter lc;
     lc.stream = st;
     lc.sync_each = std::getenv("SGM_B200_DEBUG_SYNC") != nullptr;
+    e->last_left = e->d_in[0];
+    e->last_left_stride = W;
     rc = run_frame(e, e->d_in[0], W, e->d_in[1], W, sky_l ? e->d_sky[0] : nullptr, sky_r ? e->d_sky[1] : nullptr, lc);
     e->launches = lc.launches;
     if (rc != SGM_OK) return rc;
@@ -397,6 +412,8 @@ int sgm_enqueue_device(sgm_engine* e, const void* left, size_t ls, const void* r
     LaunchCounter lc;
     lc.stream = st;
     lc.sync_each = std::getenv("SGM_B200_DEBUG_SYNC") != nullptr;
+    e->last_left = static_cast<const uint8_t*>(left);
+    e->last_left_stride = ls;
     rc = run_frame(e, static_cast<const uint8_t*>(left), ls, static_cast<const uint8_t*>(right), rs, sl, sr, lc);
     e->launches = lc.launches;
     if (rc != SGM_OK) return rc;
@@ -548,6 +565,49 @@ int sgm_get_stage_ms(sgm_engine* e, float* ms, int count) {
 }
 void* sgm_get_stream(sgm_engine* e) { return e ? (void*)e->stream : nullptr; }
 size_t sgm_device_bytes(const sgm_engine* e) { return e ? e->device_bytes : 0; }
+
+int sgm_render_debug_view(sgm_engine* e, uint8_t* dst, size_t dst_stride) {
+    int rc = ready(e);
+    if (rc != SGM_OK) return rc;
+    const size_t row_bytes = (size_t)e->iw * 3;
+    if (!dst || dst_stride < row_bytes) return fail(e, SGM_ERR_INVALID, "bad destination");
+    if (!e->d_view) CU_TRY(e, dev_alloc(e, &e->d_view, 2 * e->n * 3));
+    LaunchCounter lc;
+    lc.stream = e->stream;
+    launch_debug_view(e->d_img, e->d_final, e->d_view, e->ih, e->iw, e->D, e->stream, lc);
+    if (lc.err != cudaSuccess) return fail(e, SGM_ERR_CUDA, "debug view: %s", cudaGetErrorString(lc.err));
+    CU_TRY(e, cudaMemcpy2DAsync(dst, dst_stride, e->d_view, row_bytes, row_bytes, 2 * (size_t)e->ih, cudaMemcpyDeviceToHost, e->stream));
+    CU_TRY(e, cudaStreamSynchronize(e->stream));
+    return SGM_OK;
+}
+
+int sgm_point_cloud(sgm_engine* e, const sgm_camera* cam, double* xyz, uint8_t* intensity, size_t capacity, size_t* count) {
+    int rc = ready(e);
+    if (rc != SGM_OK) return rc;
+    if (!cam || !count) return fail(e, SGM_ERR_INVALID, "camera / count is null");
+    if (!e->last_left) return fail(e, SGM_ERR_STATE, "no frame has been processed yet");
+    const int nb = cloud_blocks((int)e->n);
+    if (!e->d_pc_counts) {
+        CU_TRY(e, dev_alloc(e, &e->d_pc_counts, (size_t)nb));
+        CU_TRY(e, dev_alloc(e, &e->d_pc_offsets, (size_t)nb + 1));
+        CU_TRY(e, dev_alloc(e, &e->d_pc_xyz, e->n * 3));
+        CU_TRY(e, dev_alloc(e, &e->d_pc_int, e->n));
+    }
+    LaunchCounter lc;
+    lc.stream = e->stream;
+    launch_point_cloud(e->d_final, e->last_left, e->last_left_stride, e->ih, e->iw, cam->fx, cam->fy, cam->cx, cam->cy, cam->baseline,
+                       cam->max_range, (float)(e->D + 1), e->p.scale, e->d_pc_counts, e->d_pc_offsets, e->d_pc_xyz, e->d_pc_int, (int)e->n,
+                       e->stream, lc);
+    if (lc.err != cudaSuccess) return fail(e, SGM_ERR_CUDA, "point cloud: %s", cudaGetErrorString(lc.err));
+    int total = 0;
+    CU_TRY(e, cudaMemcpyAsync(&total, e->d_pc_offsets + nb, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+    CU_TRY(e, cudaStreamSynchronize(e->stream));
+    *count = (size_t)total;
+    const size_t take = (size_t)total < capacity ? (size_t)total : capacity;
+    if (xyz && take) CU_TRY(e, cudaMemcpy(xyz, e->d_pc_xyz, take * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+    if (intensity && take) CU_TRY(e, cudaMemcpy(intensity, e->d_pc_int, take, cudaMemcpyDeviceToHost));
+    return SGM_OK;
+}
 
 int sgm_cost_volume_sad(int device, const uint8_t* left, const uint8_t* right, int height, int width, int max_disp, int win_h, int win_w,
                         int scale, float* out) {

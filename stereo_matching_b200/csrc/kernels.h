@@ -88,4 +88,15 @@ void launch_median_fill(const float* src, float* f, int h, int w, int d, int win
 void launch_speckle(const float* f_in, float* f_out, int* labels, int* area, int h, int w, float value, int max_size,
                     float max_dis, cudaStream_t st, LaunchCounter& lc);
 
+// ---- consumers of the result (view_kernels.cu) ---------------------------------------------------
+// Solver::show_disp + colormap (src/Solver.cpp:55-93, :652-707): out is a dense (2*h) x w x 3 BGR image.
+void launch_debug_view(const uint8_t* gray, const float* disp, uint8_t* out, int h, int w, int max_disp, cudaStream_t st,
+                       LaunchCounter& lc);
+// node.cpp:119-143: ordered list of camera-frame points (xyz doubles) + grey values; counts / offsets are scratch of
+// cloud_blocks(h*w) and cloud_blocks(h*w) + 1 ints, offsets[cloud_blocks] receives the number of points.
+int cloud_blocks(int n);
+void launch_point_cloud(const float* disp, const uint8_t* img, size_t img_stride, int h, int w, float fx, float fy, float cx, float cy,
+                        double baseline, float max_range, float invalid, int scale, int* counts, int* offsets, double* xyz,
+                        uint8_t* intensity, int capacity, cudaStream_t st, LaunchCounter& lc);
+
 }  // namespace sgmb200

@@ -15,10 +15,6 @@ public:
 
     virtual void process(Mat &img_l, Mat &img_r);
     virtual void process(Mat &img_l, Mat &img_r, Mat &sky_mask, Mat &sky_mask_beta);
-
-protected:
-    // BM decimates with source row i, not i*scale (src/BM.cpp:23-24); the debug view follows it.
-    virtual int debug_source_row(int i) const { return i; }
 };
 
 typedef std::shared_ptr<BM> BMSolverPtr;

@@ -16,6 +16,8 @@
 #include "utils.h"
 #include "cost.h"
 
+#include <vector>
+
 #include "sgm_b200.h"
 
 // Matching parameters.  Names and values are the reference's (inc/Solver.h:10-20); they are handed to the engine through
@@ -52,6 +54,11 @@ public:
     // CV_32FC1, working resolution, invalid pixels == max_disp + 1 (node.cpp:104,129).  Valid until the next process().
     virtual const Mat& get_disp() const { return filtered_disp; }
 
+    // Addition to the reference surface: the disparity -> point cloud loop of node.cpp:119-143 as one device call
+    // (same arithmetic, same raster order).  Returns the number of points.
+    size_t get_point_cloud(const CamIntrinsics &cam, double baseline, float max_range, std::vector<cv::Point3d> &pts,
+                           std::vector<uchar> &pixel);
+
 protected:
     int img_h, img_w;               // working resolution (h / s, w / s)
     int scale;
@@ -76,8 +83,6 @@ protected:
     void fetch_disparity(float *d);
     // Colour map of filtered_disp into colored_disp (src/Solver.cpp:652-707).
     void colormap();
-    // Source row of working row i when building the debug view at scale > 1 (SGM: i*scale, BM: i; src/SGM.cpp:46, src/BM.cpp:23).
-    virtual int debug_source_row(int i) const { return i * scale; }
 };
 
 typedef std::shared_ptr<Solver> SolverPtr;

@@ -7,6 +7,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <vector>
 
 namespace {
 
@@ -112,59 +113,42 @@ void Solver::fetch_disparity(float *d)
         std::memcpy(filtered_disp.ptr<float>(i), d + (size_t)i * filtered_disp.cols, filtered_disp.cols * sizeof(float));
 }
 
-// Piecewise-linear blue -> cyan -> green -> yellow -> red ramp over the disparity range; invalid pixels are black.
-// Same breakpoints and integer truncation as src/Solver.cpp:652-707.
+// Colour map of filtered_disp (blue -> cyan -> green -> yellow -> red over the disparity range, invalid = black;
+// src/Solver.cpp:652-707).  Rendered on the device by sgm_render_debug_view; this keeps the reference's protected helper.
 void Solver::colormap()
 {
-    const float gain = (float)(256 / max_disp);  // integer division first, as in the reference (:667)
-    for (int i = 0; i < filtered_disp.rows; ++i) {
-        const float *src = filtered_disp.ptr<float>(i);
-        Vec3b *dst = colored_disp.ptr<Vec3b>(i);
-        for (int j = 0; j < filtered_disp.cols; ++j) {
-            float v = src[j];
-            uchar b = 0, g = 0, r = 0;
-            if (!(v > max_disp - 1)) {
-                v *= gain;
-                if (v <= 51) {
-                    b = 255;
-                    g = (uchar)(v * 5);
-                } else if (v <= 102) {
-                    b = (uchar)(255 - (v - 51) * 5);
-                    g = 255;
-                } else if (v <= 153) {
-                    g = 255;
-                    r = (uchar)((v - 102) * 5);
-                } else if (v <= 204) {
-                    g = (uchar)(255 - uchar(128.0 * (v - 153) / 51.0 + 0.5));
-                    r = 255;
-                } else {
-                    g = (uchar)(127 - uchar(127.0 * (v - 204) / 51.0 + 0.5));
-                    r = 255;
-                }
-            }
-            dst[j][0] = b;
-            dst[j][1] = g;
-            dst[j][2] = r;
-        }
-    }
+    Mat view = Mat::zeros(img_h * 2, img_w, CV_8UC3);
+    if (sgm_render_debug_view(engine, view.ptr<uchar>(0), view.step) != SGM_OK) die("colormap", engine);
+    Mat lower = view(Rect(0, img_h - 1, img_w, img_h));
+    lower.copyTo(colored_disp);
 }
 
+// src/Solver.cpp:55-93: left image on top, colour-mapped disparity below (the lower block starts at row img_h - 1).
+// Composed by one device kernel from the engine's working-resolution left image and the final disparity.
 void Solver::show_disp(Mat &debug_view)
 {
-    colormap();
-    // working-resolution left image (the reference keeps the decimated copy from process(); here it is rebuilt on demand)
-    Mat gray(img_h, img_w, CV_8UC1);
-    for (int i = 0; i < img_h; ++i) {
-        const uchar *src = img_l.ptr<uchar>(scale == 1 ? i : debug_source_row(i));
-        uchar *dst = gray.ptr<uchar>(i);
-        for (int j = 0; j < img_w; ++j) dst[j] = src[j * scale];
-    }
-    Mat bgr;
-    cvtColor(gray, bgr, CV_GRAY2BGR);
-    // image on top, colour-mapped disparity below; the lower block starts at row img_h - 1 like src/Solver.cpp:91
     debug_view = Mat::zeros(img_h * 2, img_w, CV_8UC3);
-    Mat top = debug_view(Rect(0, 0, img_w, img_h));
-    bgr.copyTo(top);
-    Mat bottom = debug_view(Rect(0, img_h - 1, img_w, img_h));
-    colored_disp.copyTo(bottom);
+    if (sgm_render_debug_view(engine, debug_view.ptr<uchar>(0), debug_view.step) != SGM_OK) die("show_disp", engine);
+}
+
+// node.cpp:119-143 as one call: camera-frame points (raster order) and their grey values, computed on the device.
+size_t Solver::get_point_cloud(const CamIntrinsics &cam, double baseline, float max_range, std::vector<cv::Point3d> &pts,
+                               std::vector<uchar> &pixel)
+{
+    sgm_camera c;
+    c.fx = cam.fx;
+    c.fy = cam.fy;
+    c.cx = cam.cx;
+    c.cy = cam.cy;
+    c.baseline = baseline;
+    c.max_range = max_range;
+    const size_t cap = (size_t)img_h * img_w;
+    std::vector<double> xyz(cap * 3);
+    pixel.resize(cap);
+    size_t n = 0;
+    if (sgm_point_cloud(engine, &c, xyz.data(), pixel.data(), cap, &n) != SGM_OK) die("get_point_cloud", engine);
+    pixel.resize(n);
+    pts.resize(n);
+    for (size_t k = 0; k < n; ++k) pts[k] = cv::Point3d(xyz[3 * k], xyz[3 * k + 1], xyz[3 * k + 2]);
+    return n;
 }

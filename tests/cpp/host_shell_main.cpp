@@ -79,5 +79,17 @@ int main(int argc, char** argv) {
     else
         sv->process(img_l, img_r);
     write_raw(out + "_disp2.f32", sv->get_disp(), sizeof(float));
+    // node.cpp:114-143 as one call (KITTI-like intrinsics)
+    CamIntrinsics cam = {718.856f, 718.856f, 607.1928f, 185.2157f};
+    std::vector<cv::Point3d> pts;
+    std::vector<uchar> pix;
+    const size_t n = sv->get_point_cloud(cam, 0.5, 100.f, pts, pix);
+    std::printf("pointcloud size: %zu, %zu\n", pts.size(), pix.size());
+    FILE* f = std::fopen((out + "_cloud.f64").c_str(), "wb");
+    for (size_t k = 0; k < n; ++k) {
+        const double v[3] = {pts[k].x, pts[k].y, pts[k].z};
+        std::fwrite(v, sizeof(double), 3, f);
+    }
+    std::fclose(f);
     return 0;
 }

@@ -2,3 +2,11 @@
 #pragma once
 #include "global.h"
 double get_cur_ms();
+
+struct CamIntrinsics  // inc/utils.h:14-20
+{
+    float fx;
+    float fy;
+    float cx;
+    float cy;
+};

@@ -92,7 +92,8 @@ def _run_driver(tmp, algo, h, w, s, d, L, R, sky):
     disp = np.fromfile(prefix + "_disp.f32", np.float32).reshape(ih, iw)
     disp2 = np.fromfile(prefix + "_disp2.f32", np.float32).reshape(ih, iw)
     dbg = np.fromfile(prefix + "_debug.bgr", np.uint8).reshape(2 * ih, iw, 3)
-    return disp, disp2, dbg, r.stdout
+    cloud = np.fromfile(prefix + "_cloud.f64", np.float64).reshape(-1, 3)
+    return disp, disp2, dbg, cloud, r.stdout
 
 
 def _colormap(f, d):
@@ -125,7 +126,7 @@ def test_node_style_driver_matches_oracle(algo, h, w, s, d, sky):
     masks = synth.sky_masks(h // s, w // s) if sky else None
     want = restate.process(L, R, s, d, algo, *(masks or (None, None)))["f_final"]
     with tempfile.TemporaryDirectory() as tmp:
-        disp, disp2, dbg, log = _run_driver(tmp, algo, h, w, s, d, L, R, masks)
+        disp, disp2, dbg, cloud, log = _run_driver(tmp, algo, h, w, s, d, L, R, masks)
     assert bits_equal(disp, want), "get_disp() of the C++ shell differs from the oracle"
     assert bits_equal(disp2, want), "second frame on the same solver differs"
     assert "time cost" in log
@@ -134,8 +135,11 @@ def test_node_style_driver_matches_oracle(algo, h, w, s, d, sky):
     row_step = 1 if (algo == "bm" or s == 1) else s
     gray = L[::row_step][:ih, ::s][:, :iw]
     assert np.array_equal(dbg[: ih - 1, :, 0], gray[: ih - 1]) and np.array_equal(dbg[: ih - 1, :, 2], gray[: ih - 1])
-    assert np.array_equal(dbg[ih - 1: 2 * ih - 1], _colormap(want, d))
+    assert np.array_equal(dbg[ih - 1: 2 * ih - 1], _colormap(want, d)) and np.array_equal(dbg, restate.debug_view(L, want, d, s, bm_rows=(algo == "bm")))
     assert not dbg[2 * ih - 1].any()
+    # get_point_cloud(): node.cpp:119-143 on the device
+    want_xyz, _ = restate.point_cloud(want, L, d, s, 718.856, 718.856, 607.1928, 185.2157, 0.5, 100.0)
+    assert cloud.shape == want_xyz.shape and np.array_equal(cloud.view(np.uint64), want_xyz.view(np.uint64))
 
 
 def test_cost_h_probes_match_oracle_dense_volumes():

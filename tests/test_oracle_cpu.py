@@ -117,3 +117,34 @@ def test_widened_restatement_runs_d256():
     out = restate.process(L, R, 1, 256, "sgm")
     f = out["f_final"]
     assert out["disp"][0].max() <= 257 and (f <= 255).sum() > 0
+
+
+@pytest.mark.skipif(not refbind.available(), reason="compiled reference (oracle/_ref) not built")
+@pytest.mark.parametrize("algo,h,w,scale,d", [("sgm", 64, 160, 1, 64), ("sgm", 96, 200, 2, 32), ("bm", 64, 160, 1, 32)])
+def test_debug_view_restatement_vs_reference_show_disp(algo, h, w, scale, d):
+    # pins oracle/restate.py's colormap / debug_view (used to check the device rendering) against Solver::show_disp
+    L, R, _ = synth.random_dot_pair(h, w, seed=h + d, bg=3, fg=min(20, d // 2), noise=12)
+    refbind.set_threads(1)
+    view, f = refbind.show_disp(algo, L, R, scale, d)
+    if algo == "bm":
+        # the reference's BM never writes filtered_disp (src/BM.cpp:52-96): colour-map whatever buffer it returned
+        want = restate.debug_view(L, f, d, scale, bm_rows=True)
+    else:
+        want = restate.debug_view(L, f, d, scale)
+    assert np.array_equal(view, want)
+    # every branch of the colour ramp, including the double-precision segments, on a synthetic ramp
+    ramp = np.linspace(0, d + 1, 4 * 257, dtype=np.float32).reshape(4, 257)
+    cm = restate.colormap(ramp, d)
+    assert cm[ramp > d - 1].max() == 0 and (cm[ramp <= d - 1].max(axis=-1) == 255).all()
+
+
+def test_point_cloud_restatement_basics():
+    # node.cpp:119-143 restated: invalid pixels and points beyond max_range are dropped, order is raster order
+    d = 64
+    f = np.full((4, 6), d + 1, np.float32)
+    f[1, 2], f[1, 4], f[3, 0] = 10.0, 0.001, 32.5     # 0.001 px -> Z far beyond 100 m -> dropped
+    left = np.arange(24, dtype=np.uint8).reshape(4, 6)
+    xyz, inten = restate.point_cloud(f, left, d, 1, 700.0, 720.0, 3.0, 2.0)
+    assert xyz.shape == (2, 3) and list(inten) == [left[1, 2], left[3, 0]]
+    z0 = (np.float64(np.float32(700.0) + np.float32(720.0)) / 2.0) * 0.5 / (np.float64(np.float32(10.0)) + 1e-6)
+    assert xyz[0, 2] == z0 and xyz[0, 0] == np.float64(np.float32(2 - 3.0)) * z0 / np.float64(np.float32(700.0))
