@@ -1,0 +1,21 @@
+"""Small frames through every kernel, for `compute-sanitizer --tool memcheck|racecheck python tests/sanitize_small.py`
+(dev helper, not a pytest; one tool per GPU call, see B200_PROFILING.md)."""
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from stereo_matching_b200 import capi, synth  # noqa: E402
+
+for cls, h, w, s, d, sky in ((capi.SGM, 48, 100, 1, 32, True), (capi.SGM, 40, 90, 1, 128, False), (capi.BM, 48, 100, 2, 32, False),
+                             (capi.BMSad, 40, 64, 1, 32, False)):
+    L, R, _ = synth.random_dot_pair(h, w, seed=h + d, bg=3, fg=9, noise=20)
+    masks = synth.sky_masks(h // s, w // s) if sky else (None, None)
+    sv = cls(h, w, s, d)
+    f = sv.process(L, R, *masks).get_disp()
+    view = sv.debug_view()
+    xyz, inten = sv.point_cloud(300.0, 300.0, w / 2, h / 2)
+    print(cls.__name__, h, w, d, "valid", float((f <= d - 1).mean()), "points", len(xyz), "launches", sv.launches)
+    sv.close()
+print("sanitize_small done")

@@ -59,6 +59,14 @@ def test_sgm_stages_bit_exact_vs_oracle(h, w, d, scale, noise, sky):
     assert (want["f_final"] <= d - 1).any()
 
 
+@pytest.mark.parametrize("h,w,d", [(16, 16, 32), (17, 33, 32), (16, 161, 128), (40, 21, 128), (19, 75, 64), (24, 48, 256)])
+def test_sgm_small_and_ragged_sizes_vs_oracle(h, w, d):
+    # smallest accepted images, widths that leave a single-column last block in the sweeps (161 = 16*10 + 1 at D=128,
+    # 33 = 4*8 + 1 at D=32), fewer rows than rows kept in flight, W < D
+    L, R, _ = synth.random_dot_pair(h, w, seed=h * w + d, bg=2, fg=min(9, w // 3), noise=25)
+    _check_sgm_against_restatement(L, R, 1, d)
+
+
 @pytest.mark.parametrize("flags", [0, capi.FLAG_LINE_WALKERS])
 def test_sgm_four_paths_vs_oracle(flags):
     L, R, _ = synth.random_dot_pair(80, 144, seed=21, bg=4, fg=13, noise=10)
