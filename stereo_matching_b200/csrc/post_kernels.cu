@@ -169,6 +169,9 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
     extern __shared__ float ring[];  // [h][RING]
     const float vmax = (float)(d - 1);
     const int i = threadIdx.x;       // one row per thread (h <= blockDim.x)
+    const int lane = threadIdx.x & 31;
+    static_assert(NWIN <= 32, "the window must fit a warp");
+    constexpr int COOP_MAX = 2;      // up to this many holes per warp and column are filled one after the other by the whole warp
     const bool row_ok = i < h;
     const bool interior_row = i >= RH && i < h - RH;
     float* myring = ring + (size_t)(row_ok ? i : 0) * RING;
@@ -192,41 +195,83 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
         asm volatile("cp.async.commit_group;");
         asm volatile("cp.async.wait_group %0;" ::"n"(LEADB));
         __syncthreads();  // feeds of batch n - LEADB and the fills of batch n - 1 are visible
-        if (interior_row) {
+        // Holes of this batch are filled warp-cooperatively: the warp votes which of its 32 rows have a hole at column
+        // c + b, then for each such hole 25 lanes gather one window element each and the median comes from a bisection
+        // on ballots (the values are integers in [0, D-1]).  Columns b = 0 .. B-1 go in order because a fill changes what
+        // the next column of the same row sees; different rows of a batch are independent (see above).
 #pragma unroll 1
-            for (int b = 0; b < B; ++b) {
-                const int x = c + b;
-                if (x < RW || x >= w - RW) continue;
-                const float own = myring[x & (RING - 1)];
-                if (own <= vmax) continue;  // not a hole
-                int vals[NWIN];
-                int cnt = 0;
+        for (int b = 0; b < B; ++b) {
+            const int x = c + b;
+            const bool hole = interior_row && x >= RW && x < w - RW && !(myring[x & (RING - 1)] <= vmax);
+            unsigned todo = __ballot_sync(FULL_MASK, hole);
+            if (__popc(todo) > COOP_MAX) {
+                // many rows of this warp have a hole in this column (occlusion bands, the invalid left margin): every such
+                // lane fills its own hole, all of them in parallel, with the same bisection on its private window
+                if (hole) {
+                    int vals[NWIN];
+                    int cnt = 0;
 #pragma unroll
-                for (int a = -RH; a <= RH; ++a)
+                    for (int a = -RH; a <= RH; ++a)
 #pragma unroll
-                    for (int e = -RW; e <= RW; ++e) {
-                        const float v = ring[(size_t)(i + a) * RING + ((x + e) & (RING - 1))];
-                        const bool ok = v <= vmax;
-                        vals[(a + RH) * WW + (e + RW)] = ok ? (int)v : 0x7fffffff;  // float -> int truncation (:619)
-                        cnt += ok ? 1 : 0;
+                        for (int e = -RW; e <= RW; ++e) {
+                            const float v = ring[(size_t)(i + a) * RING + ((x + e) & (RING - 1))];
+                            const bool ok = v <= vmax;
+                            vals[(a + RH) * WW + (e + RW)] = ok ? (int)v : 0x7fffffff;  // float -> int truncation (:619)
+                            cnt += ok ? 1 : 0;
+                        }
+                    if (cnt > NWIN / 2) {
+                        const int need = cnt / 2 + 1;
+                        int lo = 0, hi = d - 1;
+                        while (lo < hi) {
+                            const int mid = (lo + hi) >> 1;
+                            int le = 0;
+#pragma unroll
+                            for (int q = 0; q < NWIN; ++q) le += vals[q] <= mid ? 1 : 0;
+                            if (le >= need)
+                                hi = mid;
+                            else
+                                lo = mid + 1;
+                        }
+                        const float fill = (float)lo;
+                        f[(size_t)i * w + x] = fill;
+                        myring[x & (RING - 1)] = fill;
                     }
+                }
+                __syncwarp();
+                todo = 0;
+            }
+            while (todo) {
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1;
+                const int i0 = (int)(threadIdx.x & ~31u) + src;
+                const int x0 = __shfl_sync(FULL_MASK, x, src);
+                bool ok = false;
+                int val = 0x7fffffff;
+                if (lane < NWIN) {
+                    const int a = lane / WW - RH, e = lane % WW - RW;
+                    const float v = ring[(size_t)(i0 + a) * RING + ((x0 + e) & (RING - 1))];
+                    ok = v <= vmax;
+                    if (ok) val = (int)v;  // float -> int truncation (src/Solver.cpp:619)
+                }
+                const int cnt = __popc(__ballot_sync(FULL_MASK, ok));
                 if (cnt > NWIN / 2) {
                     const int need = cnt / 2 + 1;  // sorted[cnt / 2] = smallest v with #(vals <= v) >= cnt/2 + 1
                     int lo = 0, hi = d - 1;
                     while (lo < hi) {
                         const int mid = (lo + hi) >> 1;
-                        int le = 0;
-#pragma unroll
-                        for (int q = 0; q < NWIN; ++q) le += vals[q] <= mid ? 1 : 0;
+                        const int le = __popc(__ballot_sync(FULL_MASK, val <= mid));
                         if (le >= need)
                             hi = mid;
                         else
                             lo = mid + 1;
                     }
-                    const float fill = (float)lo;
-                    f[(size_t)i * w + x] = fill;
-                    myring[x & (RING - 1)] = fill;  // later pixels of this row in this batch, and everyone after the barrier
+                    if (lane == 0) {
+                        const float fill = (float)lo;
+                        f[(size_t)i0 * w + x0] = fill;
+                        ring[(size_t)i0 * RING + (x0 & (RING - 1))] = fill;  // later columns of this row, and everyone after the barrier
+                    }
                 }
+                __syncwarp();
             }
         }
     }

@@ -204,15 +204,16 @@ __device__ __forceinline__ void mbar_init(unsigned bar, int count) {
 __device__ __forceinline__ void mbar_arrive(unsigned bar) {
     asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
 }
+constexpr unsigned MBAR_SUSPEND_NS = 2000;  // upper bound of one hardware sleep; a completed phase wakes the warp at once
 __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
     asm volatile(
         "{\n\t.reg .pred p;\n"
         "WAIT_LOOP:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"  // %2: suspend-time hint (ns): sleep, do not spin
         "@p bra WAIT_DONE;\n\t"
         "bra WAIT_LOOP;\n"
         "WAIT_DONE:\n\t}" ::"r"(bar),
-        "r"(parity)
+        "r"(parity), "r"(MBAR_SUSPEND_NS)
         : "memory");
 }
 
@@ -632,7 +633,8 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
         int device = 0;
         cudaGetDevice(&device);
         const int cap = sweep_capacity<D, PATHS, CFG>(device);
-        if (nblk * a.views > cap) views_per_launch = 1;
+        static const bool split = std::getenv("SGM_B200_SWEEP_SPLIT_VIEWS") != nullptr;
+        if (nblk * a.views > cap || split) views_per_launch = 1;
         if (nblk > cap) return false;  // image too wide for a resident row-synchronous sweep: caller falls back to line walkers
     }
     const size_t vol = (size_t)a.h * a.w * a.d;
@@ -713,6 +715,8 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
             case 2: return fused_impl<D, 8, SweepCfg<10, 6, 2>>(a, st, lc);
             case 3: return fused_impl<D, 8, SweepCfg<10, 2, 2>>(a, st, lc);
             case 4: return fused_impl<D, 8, SweepCfg<12, 4, 2>>(a, st, lc);
+            case 5: return fused_impl<D, 8, SweepCfg<10, 2, 3>>(a, st, lc);
+            case 6: return fused_impl<D, 8, SweepCfg<8, 2, 4>>(a, st, lc);
             default: break;
         }
     }
