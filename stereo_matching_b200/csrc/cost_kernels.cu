@@ -336,6 +336,91 @@ __global__ void __launch_bounds__(256) sad_volume_kernel(const uint8_t* __restri
     }
 }
 
+
+// Banded form: a block owns SADB_XC window columns (SADB_XC - 2*rw output columns) x all D disparities and walks down a
+// band of rows.  Thread (k, g) keeps the vertical sums V(x, k) = sum_a |own(y+a, x) - other(y+a, x -/+ k)| of its
+// columns in registers and slides them one row at a time (+ the entering row, - the leaving row; the image rows of the
+// window sit in a small circular shared-memory buffer with the reference's clamping already applied), publishes them
+// as uint16 and then slides a horizontal box over them for its output columns.  Every (row, x, k) absolute
+// difference is computed twice per band instead of win_h * win_w times.  The two float divisions of src/cost.cpp:29
+// come from a table indexed by the integer sum (built on the host with the same IEEE divisions) when one is given.
+constexpr int SADB_XC = 32;
+
+template <int D>
+__global__ void __launch_bounds__(256) sad_volume_band_kernel(const uint8_t* __restrict__ img_l, const uint8_t* __restrict__ img_r,
+                                                              const float* __restrict__ lut, float* __restrict__ cost, int h, int w,
+                                                              int win_h, int win_w, int scale, int band) {
+    constexpr int XC = SADB_XC, G = 256 / D, NV = XC / G;
+    static_assert(256 % D == 0 && XC % G == 0, "D must be a power of two in 8..256");
+    extern __shared__ __align__(16) unsigned char sad_sm[];
+    const int rh = win_h / 2, rw = win_w / 2, TJ = XC - 2 * rw, NR = 2 * rh + 2;
+    const int OW = XC + (D - 1) / scale + 1;
+    const int RS = (XC + OW + 3) & ~3;                       // bytes per buffered image row: [own tile | other tile]
+    uint16_t* vs = reinterpret_cast<uint16_t*>(sad_sm);      // [XC][D]
+    unsigned char* rows = sad_sm + (size_t)XC * D * 2;       // [NR][RS]
+    const int view = blockIdx.z, j0 = blockIdx.x * TJ, i0 = blockIdx.y * band, i1 = min(i0 + band, h);
+    const uint8_t* own = view ? img_r : img_l;
+    const uint8_t* other = view ? img_l : img_r;
+    const int obase = view ? j0 - rw : j0 - rw - (D - 1) / scale;
+    const int t = threadIdx.x, k = t % D, g = t / D, ks = k / scale;
+
+    // index of the other image's pixel for each of this thread's window columns (clamped like src/cost.cpp:14-25)
+    int oidx[NV];
+#pragma unroll
+    for (int n = 0; n < NV; ++n) {
+        const int xcl = min(max(j0 + g + n * G - rw, 0), w - 1);
+        oidx[n] = (view ? min(xcl + ks, w - 1) : max(xcl - ks, 0)) - obase + XC;
+    }
+    auto load_row = [&](int yy) {  // yy may lie outside the image: rows are replicated
+        const int y = min(max(yy, 0), h - 1);
+        unsigned char* dst = rows + (size_t)((yy % NR + NR) % NR) * RS;
+        for (int q = t; q < XC + OW; q += 256) {
+            const int x = q < XC ? j0 + q - rw : obase + (q - XC);
+            dst[q] = (q < XC ? own : other)[(size_t)y * w + min(max(x, 0), w - 1)];
+        }
+    };
+    auto row_ptr = [&](int yy) { return rows + (size_t)((yy % NR + NR) % NR) * RS; };
+
+    int V[NV];
+#pragma unroll
+    for (int n = 0; n < NV; ++n) V[n] = 0;
+    for (int yy = i0 - rh; yy < i0 + rh; ++yy) load_row(yy);
+    __syncthreads();
+    for (int yy = i0 - rh; yy < i0 + rh; ++yy) {
+        const unsigned char* rp = row_ptr(yy);
+#pragma unroll
+        for (int n = 0; n < NV; ++n) V[n] += abs((int)rp[g + n * G] - (int)rp[oidx[n]]);
+    }
+    const int cpg = (TJ + G - 1) / G, c0 = g * cpg, c1 = min(min(c0 + cpg, TJ), w - j0);
+    for (int i = i0; i < i1; ++i) {
+        load_row(i + rh);
+        __syncthreads();  // the entering row is in place (and every thread is done with the previous vs)
+        {
+            const unsigned char* rin = row_ptr(i + rh);
+            const unsigned char* rout = row_ptr(i - rh - 1);
+            const bool sub = i > i0;
+#pragma unroll
+            for (int n = 0; n < NV; ++n) {
+                V[n] += abs((int)rin[g + n * G] - (int)rin[oidx[n]]);
+                if (sub) V[n] -= abs((int)rout[g + n * G] - (int)rout[oidx[n]]);
+                vs[(g + n * G) * D + k] = (uint16_t)V[n];
+            }
+        }
+        __syncthreads();  // vertical sums of row i are published
+        if (c0 < c1) {
+            int acc = 0;
+            for (int b = 0; b <= 2 * rw; ++b) acc += vs[(c0 + b) * D + k];
+            float* out = cost + (((size_t)view * h + i) * w + j0 + c0) * D + k;
+            for (int cj = c0;; ++cj) {
+                *out = lut ? __ldg(lut + acc) : __fdiv_rn(__fdiv_rn((float)acc, (float)win_h), (float)win_w);
+                if (cj + 1 >= c1) break;
+                acc += (int)vs[(cj + 2 * rw + 1) * D + k] - (int)vs[cj * D + k];
+                out += D;
+            }
+        }
+    }
+}
+
 }  // namespace
 
 void launch_subsample(const uint8_t* src, size_t src_stride, int col_step, int row_step, uint8_t* dst, int ih, int iw,
@@ -411,9 +496,35 @@ void launch_vfilter(float* cost, int views, int h, int w, int d, int win, cudaSt
     lc.note("vfilter_kernel");
 }
 
-void launch_sad_volume(const uint8_t* img_l, const uint8_t* img_r, float* cost, int views, int h, int w, int d, int win_h,
-                       int win_w, int scale, cudaStream_t st, LaunchCounter& lc) {
+template <int D>
+static void launch_sad_band(const uint8_t* img_l, const uint8_t* img_r, const float* lut, float* cost, int views, int h, int w, int win_h,
+                            int win_w, int scale, cudaStream_t st) {
+    const int rh = win_h / 2, rw = win_w / 2, tj = SADB_XC - 2 * rw;
+    const int ow = SADB_XC + (D - 1) / scale + 1, rs = (SADB_XC + ow + 3) & ~3;
+    const size_t smem = (size_t)SADB_XC * D * 2 + (size_t)(2 * rh + 2) * rs;
+    const int band = h >= 256 ? 48 : 32;
+    dim3 grid((w + tj - 1) / tj, (h + band - 1) / band, views);
+    sad_volume_band_kernel<D><<<grid, 256, smem, st>>>(img_l, img_r, lut, cost, h, w, win_h, win_w, scale, band);
+}
+
+// lut (optional, device): lut[s] = (float(s) / win_h) / win_w for s = 0 .. 255 * win_h * win_w
+void launch_sad_volume(const uint8_t* img_l, const uint8_t* img_r, const float* lut, float* cost, int views, int h, int w, int d,
+                       int win_h, int win_w, int scale, cudaStream_t st, LaunchCounter& lc) {
+    static const bool legacy = std::getenv("SGM_B200_SAD_LEGACY") != nullptr;
     const int rw = win_w / 2;
+    const bool band_ok = !legacy && rw <= 12 && win_h <= 63 && (d == 8 || d == 16 || d == 32 || d == 64 || d == 128 || d == 256);
+    if (band_ok) {
+        switch (d) {
+            case 8: launch_sad_band<8>(img_l, img_r, lut, cost, views, h, w, win_h, win_w, scale, st); break;
+            case 16: launch_sad_band<16>(img_l, img_r, lut, cost, views, h, w, win_h, win_w, scale, st); break;
+            case 32: launch_sad_band<32>(img_l, img_r, lut, cost, views, h, w, win_h, win_w, scale, st); break;
+            case 64: launch_sad_band<64>(img_l, img_r, lut, cost, views, h, w, win_h, win_w, scale, st); break;
+            case 128: launch_sad_band<128>(img_l, img_r, lut, cost, views, h, w, win_h, win_w, scale, st); break;
+            default: launch_sad_band<256>(img_l, img_r, lut, cost, views, h, w, win_h, win_w, scale, st); break;
+        }
+        lc.note("sad_volume_band_kernel");
+        return;
+    }
     const size_t smem = (size_t)(SAD_TJ + 2 * rw) * d * sizeof(uint16_t);
     if (smem > 48 * 1024 || win_h > 257) {
         lc.err = cudaErrorInvalidValue;

@@ -10,6 +10,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "../../include/sgm_b200.h"
 #include "kernels.h"
@@ -45,6 +46,7 @@ struct sgm_engine {
     float* d_final = nullptr;                // [n]
     int* d_label = nullptr;                  // [n]
     int* d_area = nullptr;                   // [n]
+    float* d_sad_lut = nullptr;              // SAD block matching: (sum / win_h) / win_w for every integer sum
     float* d_halo = nullptr;                 // fused aggregation: cross-block halo ring (tagged payload)
     unsigned halo_seq = 0;                   // fused aggregation: sweep launches so far (tag source)
     int* d_error = nullptr;                  // fused aggregation: time-out flag
@@ -87,6 +89,17 @@ int fail(sgm_engine* e, int code, const char* fmt, ...) {
         if (_c != cudaSuccess) return fail((e), SGM_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(_c));   \
     } while (0)
 
+// src/cost.cpp:29 returns sum / win_h / win_w: two float divisions of an integer sum <= 255 * win_h * win_w.  The SAD
+// kernel looks the result up instead of dividing (host IEEE division == __fdiv_rn).
+std::vector<float> sad_division_table(int win_h, int win_w) {
+    std::vector<float> t((size_t)255 * win_h * win_w + 1);
+    for (size_t s = 0; s < t.size(); ++s) {
+        volatile float q = (float)s / (float)win_h;
+        t[s] = q / (float)win_w;
+    }
+    return t;
+}
+
 template <typename T>
 cudaError_t dev_alloc(sgm_engine* e, T** p, size_t count) {
     cudaError_t c = cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T));
@@ -119,6 +132,7 @@ void release(sgm_engine* e) {
     cudaFree(e->d_label);
     cudaFree(e->d_area);
     cudaFree(e->d_halo);
+    cudaFree(e->d_sad_lut);
     cudaFree(e->d_error);
     cudaFree(e->d_view);
     cudaFree(e->d_pc_counts);
@@ -240,6 +254,12 @@ int sgm_create(sgm_engine** out, const sgm_params* params) {
         if (ok) *e->h_error = 0;
         if (p.flags & SGM_FLAG_KEEP_VOLUMES) ok = ok && dev_alloc(e, &e->d_pathsum, e->views * e->N) == cudaSuccess;
     }
+    if (p.algo == SGM_ALGO_BM_SAD) {
+        const int sh = p.sad_h / p.scale, sw = p.sad_w / p.scale;
+        std::vector<float> lut = sad_division_table(sh, sw);
+        ok = ok && dev_alloc(e, &e->d_sad_lut, lut.size()) == cudaSuccess;
+        ok = ok && cudaMemcpy(e->d_sad_lut, lut.data(), lut.size() * sizeof(float), cudaMemcpyHostToDevice) == cudaSuccess;
+    }
     ok = ok && dev_alloc(e, &e->d_disp, 2 * e->n) == cudaSuccess;
     ok = ok && dev_alloc(e, &e->d_sub, 2 * e->n) == cudaSuccess;
     ok = ok && dev_alloc(e, &e->d_lr, e->n) == cudaSuccess;
@@ -280,7 +300,7 @@ int run_frame(sgm_engine* e, const uint8_t* left, size_t lstride, const uint8_t*
     launch_subsample(left, lstride, s, row_step, e->d_img, h, w, st, lc);
     launch_subsample(right, rstride, s, row_step, e->d_img + e->n, h, w, st, lc);
     if (p.algo == SGM_ALGO_BM_SAD) {
-        launch_sad_volume(e->d_img, e->d_img + e->n, e->d_cost, e->views, h, w, D, p.sad_h / s, p.sad_w / s, s, st, lc);
+        launch_sad_volume(e->d_img, e->d_img + e->n, e->d_sad_lut, e->d_cost, e->views, h, w, D, p.sad_h / s, p.sad_w / s, s, st, lc);
     } else {
         launch_blur3(e->d_img, e->d_blur, h, w, st, lc);                                   // src/Solver.cpp:124-125
         launch_census(e->d_blur, e->d_census, h, w, p.census_h / s, p.census_w / s, st, lc);  // :127-139
@@ -623,14 +643,19 @@ int sgm_cost_volume_sad(int device, const uint8_t* left, const uint8_t* right, i
     if (c == cudaSuccess) c = cudaMalloc(reinterpret_cast<void**>(&d_cost), N * sizeof(float));
     if (c == cudaSuccess) c = cudaMemcpy(d_img, left, n, cudaMemcpyHostToDevice);
     if (c == cudaSuccess) c = cudaMemcpy(d_img + n, right, n, cudaMemcpyHostToDevice);
+    float* d_lut = nullptr;
+    const std::vector<float> lut = sad_division_table(win_h, win_w);
+    if (c == cudaSuccess) c = cudaMalloc(reinterpret_cast<void**>(&d_lut), lut.size() * sizeof(float));
+    if (c == cudaSuccess) c = cudaMemcpy(d_lut, lut.data(), lut.size() * sizeof(float), cudaMemcpyHostToDevice);
     LaunchCounter lc;
     if (c == cudaSuccess) {
-        launch_sad_volume(d_img, d_img + n, d_cost, 1, height, width, max_disp, win_h, win_w, scale, nullptr, lc);
+        launch_sad_volume(d_img, d_img + n, d_lut, d_cost, 1, height, width, max_disp, win_h, win_w, scale, nullptr, lc);
         c = lc.err;
     }
     if (c == cudaSuccess) c = cudaMemcpy(out, d_cost, N * sizeof(float), cudaMemcpyDeviceToHost);
     cudaFree(d_img);
     cudaFree(d_cost);
+    cudaFree(d_lut);
     if (c != cudaSuccess) return fail(nullptr, SGM_ERR_CUDA, "sgm_cost_volume_sad: %s", cudaGetErrorString(c));
     return SGM_OK;
 }

@@ -44,7 +44,7 @@ void launch_hamming_hfilter(const uint64_t* ct_l, const uint64_t* ct_r, const ui
 // src/Solver.cpp:333-368 in place on `views` volumes.
 void launch_vfilter(float* cost, int views, int h, int w, int d, int win, cudaStream_t st, LaunchCounter& lc);
 // src/cost.cpp:4-30 (SAD) for every (pixel, d) of `views` views (view 1 = right view by symmetry).
-void launch_sad_volume(const uint8_t* img_l, const uint8_t* img_r, float* cost, int views, int h, int w, int d,
+void launch_sad_volume(const uint8_t* img_l, const uint8_t* img_r, const float* lut, float* cost, int views, int h, int w, int d,
                        int win_h, int win_w, int scale, cudaStream_t st, LaunchCounter& lc);
 
 // ---- aggregation (aggregate_kernels.cu) ------------------------------------------------------

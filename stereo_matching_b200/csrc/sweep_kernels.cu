@@ -717,6 +717,12 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
             case 4: return fused_impl<D, 8, SweepCfg<12, 4, 2>>(a, st, lc);
             case 5: return fused_impl<D, 8, SweepCfg<10, 2, 3>>(a, st, lc);
             case 6: return fused_impl<D, 8, SweepCfg<8, 2, 4>>(a, st, lc);
+            case 7: return fused_impl<D, 8, SweepCfg<17, 4, 1>>(a, st, lc);
+            case 8: return fused_impl<D, 8, SweepCfg<17, 6, 1>>(a, st, lc);
+            case 9: return fused_impl<D, 8, SweepCfg<9, 4, 2>>(a, st, lc);
+            case 10: return fused_impl<D, 8, SweepCfg<18, 4, 1>>(a, st, lc);
+            case 11: return fused_impl<D, 8, SweepCfg<18, 6, 1>>(a, st, lc);
+            case 12: return fused_impl<D, 8, SweepCfg<19, 4, 1>>(a, st, lc);
             default: break;
         }
     }
