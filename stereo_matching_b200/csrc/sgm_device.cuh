@@ -102,22 +102,30 @@ __device__ __forceinline__ void path_step_n(float (&L)[N][LaneLayout<D>::E], con
     for (int n = 0; n < N; ++n) m[n] = warp_min_f32(lm[n]);
 }
 
-// WTA + uniqueness + sub-pixel on one pixel's summed costs held across the warp.
-//   src/SGM.cpp:381-416 / src/BM.cpp:59-89: first strict minimum; first occurrence of the smallest value
-//   different from it; invalid (D+1) iff min/sec > ratio && |min_d - sec_d| > min_gap.
-//   src/Solver.cpp:577-594: parabola through S[d-1], S[d], S[d+1], clamped to D-1.
+// WTA + uniqueness + sub-pixel on one pixel's summed costs held across the warp, in two halves:
+//   wta_reduce  — the warp-wide part: first strict minimum, first occurrence of the smallest value different from it
+//                 (src/SGM.cpp:381-405 / src/BM.cpp:59-80) and the winner's two neighbours; the result is warp-uniform;
+//   wta_finish  — the scalar part on those six numbers: invalid (D+1) iff min/sec > ratio && |min_d - sec_d| > min_gap
+//                 (src/SGM.cpp:406-416), then the parabola through S[d-1], S[d], S[d+1] clamped to D-1
+//                 (src/Solver.cpp:577-594).  A caller may run it later, e.g. one lane per pixel for 32 pixels at once.
+struct WtaPick {
+    float c0, sec;     // minimum; second distinct value, +inf if there is none (costs are finite: the FLT_MAX path)
+    int min_d, sec_d;
+    float cm, cp;      // S[min_d - 1], S[min_d + 1] (0 where out of range; unused there)
+};
+
 template <int D>
-__device__ __forceinline__ void wta_pixel(const float (&S)[LaneLayout<D>::E], int lane, float ratio, int min_gap,
-                                          bool parabola, int& disp_out, float& sub_out) {
+__device__ __forceinline__ WtaPick wta_reduce(const float (&S)[LaneLayout<D>::E], int lane) {
     using LL = LaneLayout<D>;
     constexpr int E = LL::E;
     constexpr int NONE = 0x7fffffff;
+    WtaPick p;
     float lmin = S[0];
 #pragma unroll
     for (int k = 1; k < E; ++k) lmin = fminf(lmin, S[k]);
     const float gmin = warp_min_f32(lmin);
     int lidx = NONE;
-    float lsec = INFINITY;  // costs are finite, so +inf marks "no second distinct value" (sec_min_cost = FLT_MAX path)
+    float lsec = INFINITY;
 #pragma unroll
     for (int k = 0; k < E; ++k) {
         if (S[k] == gmin)
@@ -140,29 +148,42 @@ __device__ __forceinline__ void wta_pixel(const float (&S)[LaneLayout<D>::E], in
         if (dk == min_d - 1) bm = __float_as_int(S[k]);
         if (dk == min_d + 1) bp = __float_as_int(S[k]);
     }
-    bm = __reduce_or_sync(FULL_MASK, (unsigned)bm);
-    bp = __reduce_or_sync(FULL_MASK, (unsigned)bp);
+    p.c0 = gmin;
+    p.sec = gsec;
+    p.min_d = min_d;
+    p.sec_d = sec_d;
+    p.cm = __int_as_float((int)__reduce_or_sync(FULL_MASK, (unsigned)bm));
+    p.cp = __int_as_float((int)__reduce_or_sync(FULL_MASK, (unsigned)bp));
+    return p;
+}
 
-    const float c0 = gmin;
+template <int D>
+__device__ __forceinline__ void wta_finish(const WtaPick& p, float ratio, int min_gap, bool parabola, int& disp_out, float& sub_out) {
     bool invalid = false;
-    if (gsec != INFINITY)  // a second distinct value exists; otherwise sec_min_cost stays FLT_MAX and the ratio test fails
-        invalid = (__fdiv_rn(c0, gsec) > ratio) && (abs(min_d - sec_d) > min_gap);
+    if (p.sec != INFINITY)  // a second distinct value exists; otherwise sec_min_cost stays FLT_MAX and the ratio test fails
+        invalid = (__fdiv_rn(p.c0, p.sec) > ratio) && (abs(p.min_d - p.sec_d) > min_gap);
     if (invalid) {
         disp_out = D + 1;
         sub_out = (float)(D + 1);
         return;
     }
-    disp_out = min_d;
-    if (!parabola || min_d == 0 || min_d == D - 1) {
-        sub_out = (float)min_d;
+    disp_out = p.min_d;
+    if (!parabola || p.min_d == 0 || p.min_d == D - 1) {
+        sub_out = (float)p.min_d;
         return;
     }
-    const float cm = __int_as_float(bm), cp = __int_as_float(bp);
-    const float num = __fsub_rn(cm, cp);
-    const float den = __fmul_rn(2.0f, __fsub_rn(__fadd_rn(cm, cp), __fmul_rn(2.0f, c0)));
-    const float v = __fadd_rn((float)min_d, __fdiv_rn(num, den));
+    const float num = __fsub_rn(p.cm, p.cp);
+    const float den = __fmul_rn(2.0f, __fsub_rn(__fadd_rn(p.cm, p.cp), __fmul_rn(2.0f, p.c0)));
+    const float v = __fadd_rn((float)p.min_d, __fdiv_rn(num, den));
     const float cap = (float)(D - 1);
     sub_out = cap < v ? cap : v;  // std::min(v, cap)
+}
+
+template <int D>
+__device__ __forceinline__ void wta_pixel(const float (&S)[LaneLayout<D>::E], int lane, float ratio, int min_gap,
+                                          bool parabola, int& disp_out, float& sub_out) {
+    const WtaPick p = wta_reduce<D>(S, lane);
+    wta_finish<D>(p, ratio, min_gap, parabola, disp_out, sub_out);
 }
 
 }  // namespace sgmb200

@@ -323,8 +323,11 @@ __global__ void __launch_bounds__(WARPS * 32) sgm_hpair_async_kernel(const float
 // so a vector is published about one row and one step before the neighbour needs it, which hides the L2 hop.
 // PF (rows of C / A / B kept in flight per warp) is even, so the row parity is a compile-time constant of the
 // unrolled body and every shared-memory address is base + immediate.
-template <int D, int NW, bool UP, int PATHS, int PF, int MINB>
+constexpr int SWEEP_DOWN = 0, SWEEP_UP = 1, SWEEP_UP_KEEP = 2;
+
+template <int D, int NW, int MODE, int PATHS, int PF, int MINB>
 __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArgs a) {
+    constexpr bool UP = MODE != SWEEP_DOWN, KEEP_S = MODE == SWEEP_UP_KEEP;  // KEEP_S: also write the path sum S (debug tap)
     using LL = LaneLayout<D>;
     using HIO = HaloIO<D>;
     constexpr int E = LL::E;
@@ -382,9 +385,10 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
     const float* py = (DIAG || !UP) ? a.acc_b + view * a.vol_stride + first : nullptr;
     float* oa = a.acc_a + view * a.vol_stride + first;
     float* ob = (DIAG && !UP) ? a.acc_b + view * a.vol_stride + first : nullptr;
-    float* os = (UP && a.pathsum) ? a.pathsum + view * a.vol_stride + first : nullptr;
+    float* os = KEEP_S ? a.pathsum + view * a.vol_stride + first : nullptr;
     const ptrdiff_t pstep = UP ? -(ptrdiff_t)w : (ptrdiff_t)w;
-    size_t opix = view * a.img_stride + (size_t)(UP ? h - 1 : 0) * w + j;
+    const size_t opix0 = view * a.img_stride + (size_t)(UP ? h - 1 : 0) * w + j;  // output pixel of sweep row 0
+    WtaPick stash = {};  // lane l keeps the selection of sweep row (r & ~31) + l until the 32 rows are finished together
 
     // C / A / B rows stream through a per-warp shared-memory ring filled by cp.async: PF rows in flight per warp cost no
     // registers and are tracked per commit group (a deep register prefetch would alias the load scoreboards).
@@ -559,18 +563,25 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                         for (int k = 0; k < E; ++k)
                             S[k] = __fadd_rn(__fadd_rn(X[k], V[k]), __fadd_rn(__fadd_rn(Y[k], G[k]), F[k]));
                     }
-                    if (os) {
+                    if (KEEP_S) {
                         stg_vec<D>(os, S);
                         os += rstep;
                     }
-                    int dd;
-                    float sub;
-                    wta_pixel<D>(S, lane, a.ratio, a.min_gap, true, dd, sub);
-                    if (lane == 0) {
-                        a.disp[opix] = (uint16_t)dd;
-                        a.subpixel[opix] = sub;
+                    // the warp-wide half of the selection now; the scalar half (uniqueness division, parabola, stores)
+                    // once per 32 rows with one lane per row instead of 32 lanes repeating the same arithmetic
+                    const WtaPick pk = wta_reduce<D>(S, lane);
+                    if (lane == (r & 31)) stash = pk;
+                    if ((r & 31) == 31 || r == h - 1) {
+                        const int rr = (r & ~31) + lane;
+                        if (rr <= r) {
+                            int dd;
+                            float sub;
+                            wta_finish<D>(stash, a.ratio, a.min_gap, true, dd, sub);
+                            const size_t o = opix0 + (ptrdiff_t)rr * pstep;
+                            a.disp[o] = (uint16_t)dd;
+                            a.subpixel[o] = sub;
+                        }
                     }
-                    opix += pstep;
                 }
                 if (r + PF < h) fetch(u);  // slot u is free: this lane has read its own bytes back
                 asm volatile("cp.async.commit_group;" ::: "memory");
@@ -592,9 +603,9 @@ constexpr size_t sweep_ring_bytes() {
     return (size_t)CFG::NW * CFG::PF * 3 * D * sizeof(float);
 }
 
-template <int D, bool UP, int PATHS, class CFG>
+template <int D, int MODE, int PATHS, class CFG>
 cudaError_t launch_sweep(const SweepArgs& sa, int nblk, int views, bool cooperative, cudaStream_t st) {
-    auto kern = sgm_sweep_kernel<D, CFG::NW, UP, PATHS, CFG::PF, CFG::MINB>;
+    auto kern = sgm_sweep_kernel<D, CFG::NW, MODE, PATHS, CFG::PF, CFG::MINB>;
     constexpr size_t ring_bytes = sweep_ring_bytes<D, CFG>();
     cudaError_t attr = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes);  // per device: cheap, so always
     if (attr != cudaSuccess) return attr;
@@ -610,17 +621,19 @@ template <int D, int PATHS, class CFG>
 int sweep_capacity(int device) {
     static int cached[16] = {};  // per device; the answer only depends on the kernel and the device
     if (device >= 0 && device < 16 && cached[device]) return cached[device] - 1;
-    int per_sm_dn = 0, per_sm_up = 0, sms = 0, coop = 0;
-    // the ring may exceed the default 48 KB of dynamic shared memory: opt in before asking for the occupancy
-    cudaFuncSetAttribute(sgm_sweep_kernel<D, CFG::NW, false, PATHS, CFG::PF, CFG::MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)sweep_ring_bytes<D, CFG>());
-    cudaFuncSetAttribute(sgm_sweep_kernel<D, CFG::NW, true, PATHS, CFG::PF, CFG::MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                         (int)sweep_ring_bytes<D, CFG>());
+    int per_sm[3] = {0, 0, 0}, sms = 0, coop = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_dn, sgm_sweep_kernel<D, CFG::NW, false, PATHS, CFG::PF, CFG::MINB>, CFG::NW * 32, sweep_ring_bytes<D, CFG>());
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_up, sgm_sweep_kernel<D, CFG::NW, true, PATHS, CFG::PF, CFG::MINB>, CFG::NW * 32, sweep_ring_bytes<D, CFG>());
-    const int cap = coop ? sms * (per_sm_dn < per_sm_up ? per_sm_dn : per_sm_up) : 0;
+    // the ring may exceed the default 48 KB of dynamic shared memory: opt in before asking for the occupancy
+    auto ask = [&](auto kern, int& out) {
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<D, CFG>());
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&out, kern, CFG::NW * 32, sweep_ring_bytes<D, CFG>());
+    };
+    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_DOWN, PATHS, CFG::PF, CFG::MINB>, per_sm[0]);
+    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP, PATHS, CFG::PF, CFG::MINB>, per_sm[1]);
+    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP_KEEP, PATHS, CFG::PF, CFG::MINB>, per_sm[2]);
+    const int least = per_sm[0] < per_sm[1] ? (per_sm[0] < per_sm[2] ? per_sm[0] : per_sm[2]) : (per_sm[1] < per_sm[2] ? per_sm[1] : per_sm[2]);
+    const int cap = coop ? sms * least : 0;
     if (device >= 0 && device < 16) cached[device] = cap + 1;
     return cap;
 }
@@ -680,8 +693,9 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
         sa.tag_base = ++(*a.launch_seq) << 12;
         for (int v0 = 0; v0 < a.views; v0 += views_per_launch) {
             sa.view0 = v0;
-            cudaError_t e = up ? launch_sweep<D, true, PATHS, CFG>(sa, nblk, views_per_launch, PATHS == 8, st)
-                               : launch_sweep<D, false, PATHS, CFG>(sa, nblk, views_per_launch, PATHS == 8, st);
+            cudaError_t e = !up         ? launch_sweep<D, SWEEP_DOWN, PATHS, CFG>(sa, nblk, views_per_launch, PATHS == 8, st)
+                            : a.pathsum ? launch_sweep<D, SWEEP_UP_KEEP, PATHS, CFG>(sa, nblk, views_per_launch, PATHS == 8, st)
+                                        : launch_sweep<D, SWEEP_UP, PATHS, CFG>(sa, nblk, views_per_launch, PATHS == 8, st);
             if (e != cudaSuccess && lc.err == cudaSuccess) {
                 lc.err = e;
                 lc.failed = "sgm_sweep_kernel (launch)";
