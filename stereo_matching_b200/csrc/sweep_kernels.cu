@@ -356,9 +356,10 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
     const bool left_border = j == 0, right_border = j == w - 1;
     const bool f_init = swap ? right_border : left_border;  // F restarts on every row (image border on its predecessor side)
     const bool g_init = swap ? false : right_border;
-    const int f_src_w = swap ? wid + 1 : wid - 1;            // shared-memory source warp of F
+    // shared-memory source warp of F; a warp whose F restarts on every row reads its own slot (valid memory, value unused)
+    const int f_src_w = f_init ? wid : (swap ? wid + 1 : wid - 1);
     const bool g_global = DIAG && (swap || (wid == nact - 1 && blk + 1 < nblk));
-    const int g_src_w = swap ? 0 : wid + 1;                  // shared-memory source warp of G (unused when g_global / g_init)
+    const int g_src_w = (g_global || g_init) ? wid : wid + 1;  // shared-memory source warp of G (own slot when unused)
     const unsigned lane_off = lane * LL::CW * 4;
     const unsigned x0 = smem_u32(xch), m0 = smem_u32(xmin);
     const unsigned f_src = x0 + f_src_w * WARP_BYTES + f_id * VEC_BYTES + lane_off, fm_src = m0 + (f_src_w * 2 + f_id) * 4;
@@ -449,26 +450,15 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                 } else {
                     float P[3][E], mP[3];
                     // previous-row vectors: F and (unless it comes from another block) G from shared memory
-                    if (!f_init) {
-                        lds_pixel<D>(f_src + (par ^ 1u) * PAR_BYTES, P[0]);
-                        mP[0] = lds_f32(fm_src + (par ^ 1u) * MIN_PAR_BYTES);
-                    } else {
-#pragma unroll
-                        for (int k = 0; k < E; ++k) P[0][k] = C[k];  // placeholder, overwritten below
-                        mP[0] = 0.f;
-                    }
+                    // (a warp whose diagonal restarts on this row still steps a vector — its own — and drops the result below)
+                    lds_pixel<D>(f_src + (par ^ 1u) * PAR_BYTES, P[0]);
+                    mP[0] = lds_f32(fm_src + (par ^ 1u) * MIN_PAR_BYTES);
 #pragma unroll
                     for (int k = 0; k < E; ++k) P[1][k] = V[k];
                     mP[1] = mV;
                     if (!g_global) {
-                        if (!g_init) {
-                            lds_pixel<D>(g_src + (par ^ 1u) * PAR_BYTES, P[2]);
-                            mP[2] = lds_f32(gm_src + (par ^ 1u) * MIN_PAR_BYTES);
-                        } else {
-#pragma unroll
-                            for (int k = 0; k < E; ++k) P[2][k] = C[k];
-                            mP[2] = 0.f;
-                        }
+                        lds_pixel<D>(g_src + (par ^ 1u) * PAR_BYTES, P[2]);
+                        mP[2] = lds_f32(gm_src + (par ^ 1u) * MIN_PAR_BYTES);
                         path_step_n<D, 3>(P, C, mP, lane, a.P1, a.P2);
                     } else {
                         // block-edge warp: F first (a neighbouring block is waiting for it), then V and G together
