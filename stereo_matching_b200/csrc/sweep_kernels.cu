@@ -133,6 +133,29 @@ struct HaloIO {
                              : "memory");
         }
     }
+    // Early, non-blocking half of consume: the loads are issued (typically a whole step before the data is needed) and
+    // accept() later checks the tags; the L2 round trip then overlaps the work in between.
+    __device__ static __forceinline__ void peek(const unsigned long long* slot, int lane, unsigned long long (&raw)[E]) {
+        if constexpr (E == 1) {
+            asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(raw[0]) : "l"(slot + lane) : "memory");
+        } else {
+#pragma unroll
+            for (int q = 0; q < E / 2; ++q)
+                asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];"
+                             : "=l"(raw[2 * q]), "=l"(raw[2 * q + 1])
+                             : "l"(slot + (q * 32 + lane) * 2)
+                             : "memory");
+        }
+    }
+    __device__ static __forceinline__ bool accept(const unsigned long long (&raw)[E], float (&v)[E], unsigned tag) {
+        bool ok = true;
+#pragma unroll
+        for (int k = 0; k < E; ++k) {
+            ok = ok && (unsigned)(raw[k] >> 32) == tag;
+            v[k] = __uint_as_float((unsigned)raw[k]);
+        }
+        return __all_sync(FULL_MASK, ok);
+    }
     // Polls until the whole vector of `tag` has arrived; false when it timed out.
     __device__ static __forceinline__ bool consume(const unsigned long long* slot, int lane, float (&v)[E], unsigned tag) {
 #pragma unroll 1
@@ -425,6 +448,11 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                 const unsigned par = u & 1;  // == r & 1 because PF is even: a constant of the unrolled body
                 const unsigned tag = a.tag_base + (unsigned)r + 1u;
                 float F[E], G[E], C[E];
+                // block-edge warp: ask L2 now for the neighbour block's row r-1 vector (published about a row ago), so the
+                // round trip overlaps the barrier wait and the F step; the tags are checked where the vector is needed
+                unsigned long long peeked[E];
+                const bool peek_ok = DIAG && g_global && r > 0 && !dead && !(a.debug & 1);
+                if (peek_ok) HIO::peek(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, peeked);
                 asm volatile("cp.async.wait_group %0;" ::"n"(PF - 1) : "memory");  // this row's C / A / B have landed
                 lds_pixel<D>(rbase + u * SLOT_BYTES, C);
                 if (DIAG && r > 0 && !(a.debug & 2)) mbar_wait(bar, par ^ 1u);  // every warp's row r-1 vectors are in shared memory
@@ -473,7 +501,8 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                         }
                         if (f_pub) HIO::publish(f_pub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, P0[0], tag);
                         float P12[2][E], m12[2];
-                        if (!dead && !(a.debug & 1) && !HIO::consume(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, P12[1], tag - 1u)) {
+                        if (peek_ok && !HIO::accept(peeked, P12[1], tag - 1u) &&
+                            !HIO::consume(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, P12[1], tag - 1u)) {
                             dead = true;
                             if (lane == 0) atomicExch(a.error, 1);
                         }
