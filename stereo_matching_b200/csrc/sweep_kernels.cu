@@ -756,8 +756,19 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
             case 10: return fused_impl<D, 8, SweepCfg<18, 4, 1>>(a, st, lc);
             case 11: return fused_impl<D, 8, SweepCfg<18, 6, 1>>(a, st, lc);
             case 12: return fused_impl<D, 8, SweepCfg<19, 4, 1>>(a, st, lc);
+            case 13: return fused_impl<D, 8, typename DefaultCfg<D>::type>(a, st, lc);
             default: break;
         }
+        // Automatic shape: when the default would put two blocks on some SMs and one on others (rows advance in
+        // lock-step, so the crowded SMs set the pace), prefer one wide block per SM with a few SMs left over for the
+        // small kernels of the other frames in flight.  KITTI width: 2 x 66 blocks of 19 columns on 148 SMs.
+        int device = 0, sms = 0;
+        cudaGetDevice(&device);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+        using Wide = SweepCfg<19, 4, 1>;
+        using Def = typename DefaultCfg<D>::type;
+        const int wide_blocks = a.views * ((a.w + Wide::NW - 1) / Wide::NW), def_blocks = a.views * ((a.w + Def::NW - 1) / Def::NW);
+        if (def_blocks > sms && wide_blocks <= sms - 12) return fused_impl<D, 8, Wide>(a, st, lc);
     }
     return fused_impl<D, 8, typename DefaultCfg<D>::type>(a, st, lc);
 }
