@@ -759,6 +759,8 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
             case 13: return fused_impl<D, 8, typename DefaultCfg<D>::type>(a, st, lc);
             default: break;
         }
+    }
+    if constexpr (D <= 128) {
         // Automatic shape: when the default would put two blocks on some SMs and one on others (rows advance in
         // lock-step, so the crowded SMs set the pace), prefer one wide block per SM with a few SMs left over for the
         // small kernels of the other frames in flight.  KITTI width: 2 x 66 blocks of 19 columns on 148 SMs.
