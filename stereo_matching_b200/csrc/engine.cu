@@ -248,6 +248,8 @@ int sgm_create(sgm_engine** out, const sgm_params* params) {
         const size_t halo_bytes = fused_halo_bytes(e->views, iw, e->D);
         ok = ok && dev_alloc(e, &e->d_halo, halo_bytes / sizeof(float)) == cudaSuccess;
         ok = ok && cudaMemset(e->d_halo, 0, halo_bytes) == cudaSuccess;
+        // test hook: start the launch sequence of the halo tags near its wrap-around (normally reached after ~5e5 frames)
+        if (const char* s0 = std::getenv("SGM_B200_HALO_SEQ_START")) e->halo_seq = (unsigned)std::strtoul(s0, nullptr, 0);
         ok = ok && dev_alloc(e, &e->d_error, 1) == cudaSuccess;
         ok = ok && cudaMemset(e->d_error, 0, sizeof(int)) == cudaSuccess;
         ok = ok && cudaMallocHost(reinterpret_cast<void**>(&e->h_error), sizeof(int)) == cudaSuccess;

@@ -67,6 +67,20 @@ def test_sgm_small_and_ragged_sizes_vs_oracle(h, w, d):
     _check_sgm_against_restatement(L, R, 1, d)
 
 
+def test_sgm_halo_tag_sequence_wraps(monkeypatch):
+    # the cross-block exchange of the sweeps tags every vector with (launch sequence, row); the sequence wraps after 2^20
+    # sweep launches (~5e5 frames), where the ring is wiped and the numbering restarts: run frames across that point
+    monkeypatch.setenv("SGM_B200_HALO_SEQ_START", str((1 << 20) - 4))
+    h, w, d = 48, 170, 128
+    pairs = [synth.random_dot_pair(h, w, seed=90 + k, bg=3, fg=11, noise=15)[:2] for k in range(2)]
+    want = [restate.process(L, R, 1, d, "sgm")["f_final"] for L, R in pairs]
+    sv = capi.SGM(h, w, 1, d)
+    for k in range(6):  # 2 sweep launches per frame: the wrap happens inside this loop
+        sv.process(*pairs[k % 2])
+        assert bits_equal(sv.get_disp(), want[k % 2]), f"frame {k} after the tag wrap differs from the oracle"
+    sv.close()
+
+
 @pytest.mark.parametrize("flags", [0, capi.FLAG_LINE_WALKERS])
 def test_sgm_four_paths_vs_oracle(flags):
     L, R, _ = synth.random_dot_pair(80, 144, seed=21, bg=4, fg=13, noise=10)
