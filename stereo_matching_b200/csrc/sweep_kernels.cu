@@ -440,6 +440,11 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
     float V[E];
     float mV = 0.f;
     bool dead = false;  // a halo wait timed out: stop waiting, keep the barrier phases going
+    // block-edge warp: loads of the neighbour block's vector for the NEXT row, issued right after this row's vectors are
+    // published (the neighbour publishes its own early in the row, so it is usually there); checked at the top of the
+    // next row, where a miss falls back to a second look and then to polling
+    unsigned long long early[E];
+    bool early_ok = false;
     for (int r0 = 0; r0 < h; r0 += PF) {
 #pragma unroll
         for (int u = 0; u < PF; ++u) {
@@ -451,8 +456,13 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                 // block-edge warp: ask L2 now for the neighbour block's row r-1 vector (published about a row ago), so the
                 // round trip overlaps the barrier wait and the F step; the tags are checked where the vector is needed
                 unsigned long long peeked[E];
+                float Gin[E];
                 const bool peek_ok = DIAG && g_global && r > 0 && !dead && !(a.debug & 1);
-                if (peek_ok) HIO::peek(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, peeked);
+                bool got = false;
+                if (peek_ok) {
+                    if (early_ok) got = HIO::accept(early, Gin, tag - 1u);
+                    if (!got) HIO::peek(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, peeked);
+                }
                 asm volatile("cp.async.wait_group %0;" ::"n"(PF - 1) : "memory");  // this row's C / A / B have landed
                 lds_pixel<D>(rbase + u * SLOT_BYTES, C);
                 if (DIAG && r > 0 && !(a.debug & 2)) mbar_wait(bar, par ^ 1u);  // every warp's row r-1 vectors are in shared memory
@@ -501,11 +511,13 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                         }
                         if (f_pub) HIO::publish(f_pub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, P0[0], tag);
                         float P12[2][E], m12[2];
-                        if (peek_ok && !HIO::accept(peeked, P12[1], tag - 1u) &&
-                            !HIO::consume(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, P12[1], tag - 1u)) {
+                        if (peek_ok && !got && !HIO::accept(peeked, Gin, tag - 1u) &&
+                            !HIO::consume(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, Gin, tag - 1u)) {
                             dead = true;
                             if (lane == 0) atomicExch(a.error, 1);
                         }
+#pragma unroll
+                        for (int k = 0; k < E; ++k) P12[1][k] = Gin[k];
 #pragma unroll
                         for (int k = 0; k < E; ++k) P12[0][k] = V[k];
                         m12[0] = mV;
@@ -550,6 +562,8 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                 if (DIAG) {
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar);  // this warp's row r vectors are published
+                    early_ok = g_global && r + 1 < h && !dead && !(a.debug & 1);
+                    if (early_ok) HIO::peek(g_sub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, early);
                 }
                 // ---- outputs (overlap the other warps' arrival) ----
                 float X[E], Y[E];
