@@ -255,16 +255,17 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
                 }
                 const int cnt = __popc(__ballot_sync(FULL_MASK, ok));
                 if (cnt > NWIN / 2) {
-                    const int need = cnt / 2 + 1;  // sorted[cnt / 2] = smallest v with #(vals <= v) >= cnt/2 + 1
-                    int lo = 0, hi = d - 1;
-                    while (lo < hi) {
-                        const int mid = (lo + hi) >> 1;
-                        const int le = __popc(__ballot_sync(FULL_MASK, val <= mid));
-                        if (le >= need)
-                            hi = mid;
-                        else
-                            lo = mid + 1;
+                    // sorted[cnt / 2] by ranking: every window lane counts the values that sort before its own (ties broken
+                    // by lane, invalid entries are INT_MAX and sort last); the NWIN shuffles are independent, so this is
+                    // one shuffle latency plus the adds instead of log2(D) dependent ballot rounds
+                    int rank = 0;
+#pragma unroll
+                    for (int q = 0; q < NWIN; ++q) {
+                        const int o = __shfl_sync(FULL_MASK, val, q);
+                        rank += (o < val || (o == val && q < lane)) ? 1 : 0;
                     }
+                    const unsigned pick = __ballot_sync(FULL_MASK, lane < NWIN && rank == cnt / 2);
+                    const int lo = __shfl_sync(FULL_MASK, val, __ffs(pick) - 1);
                     if (lane == 0) {
                         const float fill = (float)lo;
                         f[(size_t)i0 * w + x0] = fill;
