@@ -109,34 +109,36 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------
+CPU_REF_TIMEOUT_S = 240  # one attempt of the CPU reference (a frame takes ~1.5 s on 16 threads); see cpu_reference_time
+
+
 def cpu_reference_time(pairs, steps, warmup):
     """Times the reference's own CPU implementation (oracle/_ref = unmodified /root/reference sources, OpenMP on all
-    host threads; the C restatement if the compiled reference did not travel).  One step = ONE frame."""
-    from oracle import refbind
+    host threads; the restatement if the compiled reference did not travel).  One step = ONE frame (pairs[0], seed 1234).
 
-    times = []
-    if refbind.available():
-        # all host threads this process may use: torchrun exports OMP_NUM_THREADS=1, which must not throttle the baseline
+    Runs in a child process with a time limit: the reference's speckle filter races under OpenMP
+    (src/Solver.cpp:525-553), so a run that does not come back is retried once and then reported as unavailable instead
+    of taking the bench down.  Returns (kind, cores, times_ms) or (None, cores, reason)."""
+    del pairs  # the child regenerates pair 0 (same generator and seed)
+    try:
+        cores = len(os.sched_getaffinity(0))  # torchrun exports OMP_NUM_THREADS=1, which must not throttle the baseline
+    except AttributeError:
+        cores = os.cpu_count() or 1
+    cmd = [sys.executable, os.path.join(ROOT, "tests", "run_cpu_ref.py"), str(H), str(W), str(D), str(SCALE), str(warmup + steps), str(cores)]
+    why = "not run"
+    limit = max(CPU_REF_TIMEOUT_S, 30 * (warmup + steps))
+    for attempt in range(2):
         try:
-            cores = len(os.sched_getaffinity(0))
-        except AttributeError:
-            cores = os.cpu_count() or 1
-        kind = "reference"
-        refbind.set_threads(cores)
-        # one Solver instance reused for all frames, as node.cpp does (src/Solver.cpp allocates ~2.1 GB in the ctor)
-        L, R = pairs[0]
-        times = [float(x) for x in refbind.time_process("sgm", L, R, SCALE, D, warmup + steps)[warmup:]]
-    else:
-        from oracle import restate
-
-        kind, cores = "port", os.cpu_count() or 1
-        for k in range(warmup + steps):
-            L, R = pairs[k % len(pairs)]
-            t0 = time.perf_counter()
-            restate.process(L, R, SCALE, D, "sgm", taps=("f_final",))
-            if k >= warmup:
-                times.append((time.perf_counter() - t0) * 1e3)
-    return kind, cores, times
+            r = subprocess.run(cmd, capture_output=True, text=True, timeout=limit)
+        except subprocess.TimeoutExpired:
+            why = f"no answer within {limit} s (attempt {attempt + 1})"
+            continue
+        last = [ln for ln in r.stdout.splitlines() if ln.startswith("{")]
+        if r.returncode == 0 and last:
+            j = json.loads(last[-1])
+            return j["kind"], j["cores"], [float(x) for x in j["ms"][warmup:]]
+        why = f"rc {r.returncode}: {r.stderr.strip()[-200:]}"
+    return None, cores, why
 
 
 def run_reference_arm(args, rank, world):
@@ -144,6 +146,9 @@ def run_reference_arm(args, rank, world):
         return  # rank 0 alone runs the CPU reference; the others exit 0 without work
     pairs = make_pairs()
     kind, cores, times = cpu_reference_time(pairs, args.steps, max(args.warmup, 1))
+    if kind is None:
+        print(json.dumps({"impl": "reference", "unavailable": f"CPU reference did not finish: {times}"}), flush=True)
+        return
     total_s = sum(times) / 1e3
     fps = len(times) / total_s
     line = {
@@ -364,6 +369,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    # watchdog: a bench that does not finish must say where it is stuck and exit, not sit until somebody kills it
+    import faulthandler
+    faulthandler.dump_traceback_later(int(os.environ.get("SGM_B200_BENCH_WATCHDOG_S", "1200")), exit=True)
 
     rank, world, local, dist = dist_setup(args)
     if args.impl == "reference":
@@ -400,10 +408,13 @@ def main():
             "device_bytes_per_engine": r["device_bytes"],
         }
         if not args.no_cpu_baseline and world == 1:
-            kind, cores, times = cpu_reference_time(make_pairs()[:1], 2, 1)
-            cfps = len(times) / (sum(times) / 1e3)
-            line["cpu_baseline"] = {"value": cfps, "unit": "frames/s", "cores": cores, "kind": kind,
-                                    "sample": f"{len(times)} frames of the same 1242x375 D=128 workload after 1 warm-up, SGM::process (src/SGM.cpp:32-826), OpenMP on all host threads"}
+            kind, cores, times = cpu_reference_time(None, 2, 1)
+            if kind is None:
+                line["cpu_baseline"] = {"value": None, "unit": "frames/s", "cores": cores, "kind": "reference", "sample": f"unavailable: {times}"}
+            else:
+                cfps = len(times) / (sum(times) / 1e3)
+                line["cpu_baseline"] = {"value": cfps, "unit": "frames/s", "cores": cores, "kind": kind,
+                                        "sample": f"{len(times)} frames of the same 1242x375 D=128 workload after 1 warm-up, SGM::process (src/SGM.cpp:32-826), OpenMP on all host threads"}
         else:
             line["cpu_baseline"] = None
         if not args.no_cpu_baseline and world == 1:

@@ -228,15 +228,23 @@ __device__ __forceinline__ void mbar_arrive(unsigned bar) {
     asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(bar) : "memory");
 }
 constexpr unsigned MBAR_SUSPEND_NS = 2000;  // upper bound of one hardware sleep; a completed phase wakes the warp at once
-__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+// Bounded: a phase that never completes (a lost arrival would be a bug, a block that never became resident a launch
+// problem) must end as an error code of the frame, not as a hung GPU.  After 2^20 tries of up to 2 us each the warp
+// records error 2 and exits; the warps waiting for it follow the same way, so the launch ends within seconds.  The
+// counter lives inside the PTX loop: the path of a wait that succeeds at once is one instruction longer than unbounded.
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity, int* err) {
     asm volatile(
-        "{\n\t.reg .pred p;\n"
+        "{\n\t.reg .pred p, q;\n\t.reg .u32 n;\n\tmov.u32 n, 0;\n"
         "WAIT_LOOP:\n\t"
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"  // %2: suspend-time hint (ns): sleep, do not spin
         "@p bra WAIT_DONE;\n\t"
-        "bra WAIT_LOOP;\n"
+        "add.u32 n, n, 1;\n\t"
+        "setp.lt.u32 q, n, 1048576;\n\t"
+        "@q bra WAIT_LOOP;\n\t"
+        "st.global.u32 [%3], 2;\n\t"
+        "exit;\n"
         "WAIT_DONE:\n\t}" ::"r"(bar),
-        "r"(parity), "r"(MBAR_SUSPEND_NS)
+        "r"(parity), "r"(MBAR_SUSPEND_NS), "l"(err)
         : "memory");
 }
 
@@ -465,7 +473,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                 }
                 asm volatile("cp.async.wait_group %0;" ::"n"(PF - 1) : "memory");  // this row's C / A / B have landed
                 lds_pixel<D>(rbase + u * SLOT_BYTES, C);
-                if (DIAG && r > 0 && !(a.debug & 2)) mbar_wait(bar, par ^ 1u);  // every warp's row r-1 vectors are in shared memory
+                if (DIAG && r > 0 && !(a.debug & 2)) mbar_wait(bar, par ^ 1u, a.error);  // every warp's row r-1 vectors are in shared memory
                 // ---- the three recurrences of this pixel (P[0] = F, P[1] = V, P[2] = G) ----
                 // F, V and G only depend on the previous row, not on each other, so they advance together
                 // (path_step_n) unless G has to wait for a neighbouring block: then F goes first and is published,
