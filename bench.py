@@ -36,11 +36,21 @@ H, W, D, SCALE = 375, 1242, 128, 1
 FRAMES_PER_STEP = 8
 N_PAIRS = 8
 WORKLOAD = "configs[2]: 1242x375 random-dot pairs, census 7x9 + recursive box + 8-path SGM D=128, sub-pixel, LR-check, median, speckle"
+# --mode: the headline is "reference" (the reference's float32 arithmetic with its recursive cost filter).  "nofilter" switches
+# the cost filter off (window 1x1, still float32); "integer" is the same computation on 16-bit integer volumes with DPX
+# instructions (SGM_FLAG_INTEGER: identical results to "nofilter", tests/test_parity_gpu.py).  Secondary lines, not the metric.
+MODES = {
+    "reference": dict(over={}, flags=0, bytes_per_disp_px=96.0, dtype="f32", workload=WORKLOAD),
+    "nofilter": dict(over=dict(box_w=1, box_h=1), flags=0, bytes_per_disp_px=96.0, dtype="f32",
+                     workload=WORKLOAD.replace("recursive box", "no cost filter")),
+    "integer": dict(over=dict(box_w=1, box_h=1), flags=8, bytes_per_disp_px=48.0, dtype="s16",
+                    workload=WORKLOAD.replace("recursive box", "no cost filter") + "; INTEGER mode: s16x2 volumes, DPX min-plus"),
+}
 
 
-def config_dict(n_gpus, inflight):
+def config_dict(n_gpus, inflight, mode="reference"):
     return {
-        "workload": WORKLOAD,
+        "workload": MODES[mode]["workload"],
         "width": W, "height": H, "max_disp": D, "paths": 8, "scale": SCALE,
         "frames_per_step": FRAMES_PER_STEP, "distinct_pairs": N_PAIRS, "inflight_frames_per_gpu": inflight,
         "sharding": f"independent pairs round-robin over {n_gpus} GPU(s), no collective",
@@ -240,8 +250,9 @@ def run_gpu_arm(args, rank, world, local, dist):
     torch.cuda.set_device(device)
     pairs = make_pairs()
     inflight = args.inflight
-    engines = [capi.SGM(H, W, SCALE, D, device=local) for _ in range(inflight)]
-    probe = capi.SGM(H, W, SCALE, D, device=local, flags=capi.FLAG_STAGE_TIMING)
+    mode = MODES[args.mode]
+    engines = [capi.SGM(H, W, SCALE, D, device=local, flags=mode["flags"], **mode["over"]) for _ in range(inflight)]
+    probe = capi.SGM(H, W, SCALE, D, device=local, flags=capi.FLAG_STAGE_TIMING | mode["flags"], **mode["over"])
     dev_pairs = [(torch.from_numpy(L).to(device), torch.from_numpy(R).to(device)) for L, R in pairs]
     out = np.empty((H, W), np.float32)
     torch.cuda.synchronize(device)
@@ -367,6 +378,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--inflight", type=int, default=3, help="frames in flight per GPU (engine handles)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mode", default="reference", choices=sorted(MODES), help="secondary lines: nofilter / integer (see MODES)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     # watchdog: a bench that does not finish must say where it is stuck and exit, not sit until somebody kills it
@@ -389,19 +401,20 @@ def main():
         fps_e2e = total_frames / (r["ms_e2e"] / 1e3)
         peak, peak_src = load_peaks()
         agg_ms = r["stage_ms"]["aggregate"]
-        alg_bytes = 96.0 * n_px  # 48 B per disp.px per pass, two passes per frame
+        # 48 B per disp.px per pass, two passes per frame (float32 volumes); 24 B per pass with 16-bit volumes
+        alg_bytes = MODES[args.mode]["bytes_per_disp_px"] * n_px
         achieved = alg_bytes / (agg_ms / 1e3) / 1e9
         line = {
             "metric": "sgm_frames_per_s", "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": r["ms_value"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": config_dict(world, r["inflight"]),
+            "dtype": MODES[args.mode]["dtype"], "data": "synthetic", "config": config_dict(world, r["inflight"], args.mode),
             "gdisp_px_per_s": fps * n_px / 1e9,
             "e2e": {"value": fps_e2e, "unit": "frames/s", "h2d_bytes_per_step": 2 * H * W * FRAMES_PER_STEP,
                     "d2h_bytes_per_step": 4 * H * W * FRAMES_PER_STEP, "gdisp_px_per_s": fps_e2e * n_px / 1e9},
             "gpu_launches": r["launches"],
             "roofline": {"kernel": "aggregation stage = sgm_hpair_async_kernel + sgm_sweep_kernel<DOWN> + sgm_sweep_kernel<UP> (3 launches per frame, both views per launch; the up sweep ends in the fused sum/WTA/uniqueness/sub-pixel epilogue)",
                          "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": load_traffic(), "peak_source": peak_src, "algorithmic_bytes_per_frame": alg_bytes,
+                         "traffic": load_traffic() if args.mode == "reference" else None, "peak_source": peak_src, "algorithmic_bytes_per_frame": alg_bytes,
                          "ms_per_frame": agg_ms, "timing": "engine-side CUDA events on the launching stream, frames run serially"},
             "stage_ms_per_frame": r["stage_ms"],
             "clocks": r["clocks"],

@@ -71,6 +71,12 @@ typedef struct sgm_params {
 
 #define SGM_FLAG_KEEP_VOLUMES 0x1u /* keep the summed path volume S of both views readable through sgm_get_tap (debug; costs 4 B per disp.px) */
 #define SGM_FLAG_LINE_WALKERS 0x4u /* aggregate with the independent line-walker kernels (8 launches, 88 B/disp.px) instead of the fused sweeps */
+/* Integer / DPX mode (north_star): with the cost filter switched off (box_w / scale == box_h / scale == 1) and no
+ * sky mask every number on the reference's path (src/SGM.cpp:82-418) is an integer < 2^15 that float32 holds exactly, so the
+ * engine keeps the volumes as 16-bit integers (half the bytes) and runs the min-plus recurrences on s16x2 pairs with the DPX
+ * instructions VIMNMX3 / VIADDMNMX.  Results are IDENTICAL to the float path under the same parameters (tested tap by tap);
+ * sgm_create rejects parameter sets for which that would not hold (SGM_ERR_UNSUPPORTED). */
+#define SGM_FLAG_INTEGER 0x8u
 #define SGM_FLAG_STAGE_TIMING 0x2u /* record CUDA events around the pipeline stages on the engine's stream (sgm_get_stage_ms) */
 
 /* Buffers readable after a frame, for parity tests and debugging (the reference keeps the same data in

@@ -108,6 +108,18 @@ def process(left, right, scale, d, algo="sgm", sky_l=None, sky_r=None, taps=LIGH
     return out
 
 
+def aggregate_u16(cost, P1=10, P2=100, paths=8) -> np.ndarray:
+    """orc_aggregate_u16: the eight SGM paths and their sum in 16-bit integers on an (h, w, d) uint16 cost volume."""
+    cost = np.ascontiguousarray(cost, np.uint16)
+    h, w, d = cost.shape
+    S = np.zeros_like(cost)
+    f = lib().orc_aggregate_u16
+    f.restype = None
+    f.argtypes = [C.c_void_p] + [C.c_int] * 6 + [C.c_void_p]
+    f(cost.ctypes.data, h, w, d, P1, P2, paths, S.ctypes.data)
+    return S
+
+
 def fnv1a64(buf) -> str:
     a = np.ascontiguousarray(buf)
     return f"{lib().orc_fnv1a64(a.ctypes.data, a.nbytes):016x}"

@@ -302,6 +302,61 @@ void orc_aggregate(const float* cost, int h, int w, int d, int P1, int P2, int p
     free(minL);
 }
 
+/* Integer restatement of orc_aggregate (the engine's SGM_FLAG_INTEGER mode): the same eight paths
+ * (src/SGM.cpp:82-369) and their sum (:386-390) in 16-bit integer arithmetic.  It applies when the costs are small
+ * non-negative integers (raw Hamming costs: cost filter window 1x1, no sky fill); the float loops of the reference then
+ * only ever produce integers < 2^24, every float operation is exact, and this function returns the same numbers as
+ * orc_aggregate (tests/test_oracle_cpu.py checks that), which is what makes the integer mode comparable with the
+ * reference at all. */
+static void path_pixel_u16(const uint16_t* C, const uint16_t* Lp, int has_prev, int min_prev, int d, int P1, int P2,
+                           uint16_t* L, uint16_t* min_out) {
+    int m = 0x7fffffff;
+    for (int k = 0; k < d; ++k) {
+        int v;
+        if (!has_prev) {
+            v = C[k];
+        } else {
+            const int km = k - 1 < 0 ? 0 : k - 1;
+            const int kp = k + 1 > d - 1 ? d - 1 : k + 1;
+            v = Lp[k];
+            if (Lp[km] + P1 < v) v = Lp[km] + P1;
+            if (Lp[kp] + P1 < v) v = Lp[kp] + P1;
+            if (min_prev + P2 < v) v = min_prev + P2;
+            v += C[k] - min_prev;
+        }
+        L[k] = (uint16_t)v;
+        if (v < m) m = v;
+    }
+    *min_out = (uint16_t)m;
+}
+
+void orc_aggregate_u16(const uint16_t* cost, int h, int w, int d, int P1, int P2, int paths, uint16_t* S) {
+    static const int DI[8] = {0, 0, 1, -1, 1, 1, -1, -1};
+    static const int DJ[8] = {1, -1, 0, 0, 1, -1, 1, -1};
+    const size_t n = (size_t)h * w, nd = n * d;
+    uint16_t* L = (uint16_t*)malloc(nd * sizeof(uint16_t));
+    uint16_t* minL = (uint16_t*)malloc(n * sizeof(uint16_t));
+    memset(S, 0, nd * sizeof(uint16_t));
+    for (int p = 0; p < paths; ++p) {
+        const int di = DI[p], dj = DJ[p];
+        /* pixels in the direction of travel: the predecessor (i - di, j - dj) is always finished first */
+        for (int si = 0; si < h; ++si) {
+            const int i = di >= 0 ? si : h - 1 - si;
+            for (int sj = 0; sj < w; ++sj) {
+                const int j = dj >= 0 ? sj : w - 1 - sj;
+                const int ip = i - di, jp = j - dj;
+                const int has_prev = ip >= 0 && ip < h && jp >= 0 && jp < w;
+                path_pixel_u16(cost + IDX3(i, j, 0, w, d), has_prev ? L + IDX3(ip, jp, 0, w, d) : NULL, has_prev,
+                               has_prev ? minL[(size_t)ip * w + jp] : 0, d, P1, P2, L + IDX3(i, j, 0, w, d),
+                               &minL[(size_t)i * w + j]);
+            }
+        }
+        for (size_t t = 0; t < nd; ++t) S[t] = (uint16_t)(S[t] + L[t]);
+    }
+    free(L);
+    free(minL);
+}
+
 /* src/SGM.cpp:373-418 (min_gap = 1) and src/BM.cpp:52-91 (min_gap = 2): first strict minimum, first
  * occurrence of the smallest value different from it, invalid (= D+1) iff
  * min/sec > ratio && |min_d - sec_d| > min_gap.  sec_d is deliberately carried across pixels in raster

@@ -74,6 +74,8 @@ void orc_sad_volume(const uint8_t* img_l, const uint8_t* img_r, int h, int w, in
 void orc_box_filter_h(float* cost, int h, int w, int d, int win);
 void orc_box_filter_v(float* cost, int h, int w, int d, int win);
 void orc_aggregate(const float* cost, int h, int w, int d, int P1, int P2, int paths, float* S);
+/* Integer (16-bit) form of orc_aggregate for integer-valued costs: the oracle of the engine's SGM_FLAG_INTEGER mode. */
+void orc_aggregate_u16(const uint16_t* cost, int h, int w, int d, int P1, int P2, int paths, uint16_t* S);
 void orc_wta(const float* S, int h, int w, int d, float ratio, int min_gap, uint16_t* disp);
 void orc_subpixel(const uint16_t* disp, const float* S, int h, int w, int d, float* out);
 void orc_lr_check(float* fl, const float* fr, int h, int w, int d, int scale, float thresh);

@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libsgm_b200.so")
 
 ALGO_SGM, ALGO_BM, ALGO_BM_SAD = 0, 1, 2
-FLAG_KEEP_VOLUMES, FLAG_STAGE_TIMING, FLAG_LINE_WALKERS = 1, 2, 4
+FLAG_KEEP_VOLUMES, FLAG_STAGE_TIMING, FLAG_LINE_WALKERS, FLAG_INTEGER = 1, 2, 4, 8
 TAP = dict(census=0, cost=1, pathsum=2, disp=3, subpixel=4, lr=5, median=6, final=7, blur=8)
 _TAP_DTYPE = dict(census=np.uint64, cost=np.float32, pathsum=np.float32, disp=np.uint16, subpixel=np.float32,
                   lr=np.float32, median=np.float32, final=np.float32, blur=np.uint8)

@@ -483,6 +483,77 @@ void launch_hamming_hfilter(const uint64_t* ct_l, const uint64_t* ct_r, const ui
     lc.note("hamming_hfilter_kernel");
 }
 
+// Integer mode: the raw Hamming volume of src/Solver.cpp:143-248 (no sky mask, no cost filter) as
+// s16x2 words, two disparities {2k, 2k+1} per 32-bit word, the layout S16x2Arith works on.  Block = (row, view); both
+// census rows are staged in shared memory like hamming_hfilter_row_kernel does; a thread produces two adjacent words
+// (four disparities) per step and stores them as one 8-byte access, fully coalesced along d.
+__global__ void __launch_bounds__(256) hamming_s16x2_kernel(const uint64_t* __restrict__ ct_l, const uint64_t* __restrict__ ct_r,
+                                                            uint2* __restrict__ cost, int h, int w, int d, int scale) {
+    extern __shared__ __align__(16) unsigned char hsm[];
+    const int i = blockIdx.x, view = blockIdx.y;
+    uint64_t* rowA = reinterpret_cast<uint64_t*>(hsm);
+    uint64_t* rowB = rowA + w;  // view 0: right row padded on the left by d entries; view 1: left row padded on the right
+    const uint64_t* srcA = (view == 0 ? ct_l : ct_r) + (size_t)i * w;
+    const uint64_t* srcB = (view == 0 ? ct_r : ct_l) + (size_t)i * w;
+    for (int t = threadIdx.x; t < w; t += blockDim.x) rowA[t] = __ldg(srcA + t);
+    for (int t = threadIdx.x; t < w + d; t += blockDim.x) rowB[t] = __ldg(srcB + (view == 0 ? max(t - d, 0) : min(t, w - 1)));
+    __syncthreads();
+    const int q = d / 4;                      // 8-byte stores per pixel; a power of two <= 64
+    const int g = threadIdx.x & (q - 1);      // this thread's group of four disparities 4g .. 4g+3
+    const int p = threadIdx.x / q, np = blockDim.x / q;
+    uint2* out = cost + ((size_t)view * h + i) * (size_t)w * q + g;
+    auto emit = [&](int j, uint64_t a, uint64_t b0, uint64_t b1, uint64_t b2, uint64_t b3) {
+        const unsigned c0 = __popcll(a ^ b0), c1 = __popcll(a ^ b1), c2 = __popcll(a ^ b2), c3 = __popcll(a ^ b3);
+        out[(size_t)j * q] = make_uint2(c0 | (c1 << 16), c2 | (c3 << 16));
+    };
+    if (scale != 1) {  // general form: four look-ups per step
+        for (int j = p; j < w; j += np) {
+            uint64_t b[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int shift = (4 * g + e) / scale;
+                b[e] = rowB[view == 0 ? j + d - shift : j + shift];
+            }
+            emit(j, rowA[j], b[0], b[1], b[2], b[3]);
+        }
+        return;
+    }
+    // scale 1: the thread walks a contiguous run of columns; moving one column on shifts the four partners by one entry,
+    // so only one of them is new (a shift register instead of four shared-memory reads per step)
+    const int seg = (w + np - 1) / np, j0 = p * seg, j1 = min(w, j0 + seg);
+    if (j0 >= j1) return;
+    if (view == 0) {  // partner of disparity k at column j: rowB[j + d - k]
+        const uint64_t* pb = rowB + d - 4 * g;
+        uint64_t b1 = pb[j0 - 1], b2 = pb[j0 - 2], b3 = pb[j0 - 3];
+        for (int j = j0; j < j1; ++j) {
+            const uint64_t b0 = pb[j];
+            emit(j, rowA[j], b0, b1, b2, b3);
+            b3 = b2, b2 = b1, b1 = b0;
+        }
+    } else {          // rowB[j + k]
+        const uint64_t* pb = rowB + 4 * g;
+        uint64_t b0 = pb[j0], b1 = pb[j0 + 1], b2 = pb[j0 + 2];
+        for (int j = j0; j < j1; ++j) {
+            const uint64_t b3 = pb[j + 3];
+            emit(j, rowA[j], b0, b1, b2, b3);
+            b0 = b1, b1 = b2, b2 = b3;
+        }
+    }
+}
+
+void launch_hamming_s16x2(const uint64_t* ct_l, const uint64_t* ct_r, void* cost, int views, int h, int w, int d, int scale,
+                          cudaStream_t st, LaunchCounter& lc) {
+    const size_t smem = (size_t)(2 * w + d) * sizeof(uint64_t);
+    if (smem > 200 * 1024 || d % 4) {
+        lc.err = cudaErrorInvalidValue;
+        lc.failed = "hamming_s16x2_kernel (row too wide)";
+        return;
+    }
+    if (smem > 48 * 1024) cudaFuncSetAttribute(hamming_s16x2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    hamming_s16x2_kernel<<<dim3(h, views), 256, smem, st>>>(ct_l, ct_r, static_cast<uint2*>(cost), h, w, d, scale);
+    lc.note("hamming_s16x2_kernel");
+}
+
 void launch_vfilter(float* cost, int views, int h, int w, int d, int win, cudaStream_t st, LaunchCounter& lc) {
     dim3 grid((unsigned)(((size_t)w * d + 255) / 256), views);
     switch (win) {

@@ -24,6 +24,8 @@ struct sgm_engine {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[SGM_STAGE_COUNT + 1] = {};
     bool timing = false, have_result = false, result_on_host = false, busy = false;
+    bool integer = false;  // SGM_FLAG_INTEGER: volumes hold s16x2 words (two disparities per 32-bit word)
+    size_t vol_words = 0;  // 32-bit words per view of a volume: N (float mode) or N / 2 (integer mode)
     int launches = 0;
     float stage_ms[SGM_STAGE_COUNT] = {};
     size_t device_bytes = 0;
@@ -211,6 +213,14 @@ int sgm_create(sgm_engine** out, const sgm_params* params) {
         if ((size_t)(32 + 2 * (sw / 2)) * p.max_disp * 2 > 48 * 1024)
             return fail(nullptr, SGM_ERR_UNSUPPORTED, "SAD window too wide for this max_disp");
     }
+    if (p.flags & SGM_FLAG_INTEGER) {
+        // every value on the path must be an integer that fits 15 bits: raw Hamming costs (no cost filter), no sky fill
+        if (p.algo != SGM_ALGO_SGM) return fail(nullptr, SGM_ERR_UNSUPPORTED, "SGM_FLAG_INTEGER needs SGM_ALGO_SGM");
+        if (bw != 1 || bh != 1) return fail(nullptr, SGM_ERR_UNSUPPORTED, "SGM_FLAG_INTEGER needs box_w / scale == box_h / scale == 1 (no cost filter)");
+        if (p.max_disp < 64) return fail(nullptr, SGM_ERR_UNSUPPORTED, "SGM_FLAG_INTEGER needs max_disp 64, 128 or 256");
+        if (p.P1 < 0 || p.P2 < p.P1 || 8 * (62 + p.P2) > 32767) return fail(nullptr, SGM_ERR_UNSUPPORTED, "SGM_FLAG_INTEGER needs 0 <= P1 <= P2 <= 4033");
+        if (p.flags & SGM_FLAG_LINE_WALKERS) return fail(nullptr, SGM_ERR_UNSUPPORTED, "SGM_FLAG_INTEGER has no line-walker schedule");
+    }
     int ndev = 0;
     cudaError_t c = cudaGetDeviceCount(&ndev);
     if (c != cudaSuccess || ndev <= 0)
@@ -228,6 +238,8 @@ int sgm_create(sgm_engine** out, const sgm_params* params) {
     e->n = (size_t)ih * iw;
     e->N = e->n * e->D;
     e->timing = (p.flags & SGM_FLAG_STAGE_TIMING) != 0;
+    e->integer = (p.flags & SGM_FLAG_INTEGER) != 0;
+    e->vol_words = e->integer ? e->N / 2 : e->N;
     const size_t full = (size_t)p.height * p.width;
     bool ok = cudaSetDevice(p.device) == cudaSuccess;
     ok = ok && cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess;
@@ -241,10 +253,10 @@ int sgm_create(sgm_engine** out, const sgm_params* params) {
     ok = ok && dev_alloc(e, &e->d_img, 2 * e->n) == cudaSuccess;
     ok = ok && dev_alloc(e, &e->d_blur, 2 * e->n) == cudaSuccess;
     ok = ok && dev_alloc(e, &e->d_census, 2 * e->n) == cudaSuccess;
-    ok = ok && dev_alloc(e, &e->d_cost, e->views * e->N) == cudaSuccess;
+    ok = ok && dev_alloc(e, &e->d_cost, e->views * e->vol_words) == cudaSuccess;
     if (p.algo == SGM_ALGO_SGM) {
-        ok = ok && dev_alloc(e, &e->d_acc_a, e->views * e->N) == cudaSuccess;
-        ok = ok && dev_alloc(e, &e->d_acc_b, e->views * e->N) == cudaSuccess;
+        ok = ok && dev_alloc(e, &e->d_acc_a, e->views * e->vol_words) == cudaSuccess;
+        ok = ok && dev_alloc(e, &e->d_acc_b, e->views * e->vol_words) == cudaSuccess;
         const size_t halo_bytes = fused_halo_bytes(e->views, iw, e->D);
         ok = ok && dev_alloc(e, &e->d_halo, halo_bytes / sizeof(float)) == cudaSuccess;
         ok = ok && cudaMemset(e->d_halo, 0, halo_bytes) == cudaSuccess;
@@ -254,7 +266,7 @@ int sgm_create(sgm_engine** out, const sgm_params* params) {
         ok = ok && cudaMemset(e->d_error, 0, sizeof(int)) == cudaSuccess;
         ok = ok && cudaMallocHost(reinterpret_cast<void**>(&e->h_error), sizeof(int)) == cudaSuccess;
         if (ok) *e->h_error = 0;
-        if (p.flags & SGM_FLAG_KEEP_VOLUMES) ok = ok && dev_alloc(e, &e->d_pathsum, e->views * e->N) == cudaSuccess;
+        if (p.flags & SGM_FLAG_KEEP_VOLUMES) ok = ok && dev_alloc(e, &e->d_pathsum, e->views * e->vol_words) == cudaSuccess;
     }
     if (p.algo == SGM_ALGO_BM_SAD) {
         const int sh = p.sad_h / p.scale, sw = p.sad_w / p.scale;
@@ -306,9 +318,13 @@ int run_frame(sgm_engine* e, const uint8_t* left, size_t lstride, const uint8_t*
     } else {
         launch_blur3(e->d_img, e->d_blur, h, w, st, lc);                                   // src/Solver.cpp:124-125
         launch_census(e->d_blur, e->d_census, h, w, p.census_h / s, p.census_w / s, st, lc);  // :127-139
+        if (e->integer)
+            launch_hamming_s16x2(e->d_census, e->d_census + e->n, e->d_cost, e->views, h, w, D, s, st, lc);  // :143-248, raw
+        else {
         launch_hamming_hfilter(e->d_census, e->d_census + e->n, sky_l, sky_r, e->d_cost, e->views, h, w, D, s, p.box_w / s, st,
                                lc);                                                          // :143-248, :296-330
         launch_vfilter(e->d_cost, e->views, h, w, D, p.box_h / s, st, lc);                  // :333-368
+        }
     }
 
     // ---- aggregation / selection ----
@@ -333,9 +349,12 @@ int run_frame(sgm_engine* e, const uint8_t* left, size_t lstride, const uint8_t*
         a.halo = e->d_halo;
         a.launch_seq = &e->halo_seq;
         a.error = e->d_error;
+        a.packed16 = e->integer ? 1 : 0;
         // fused three-launch schedule (sweep_kernels.cu) unless disabled or the image is too wide for a resident sweep
         const bool want_fused = !(p.flags & SGM_FLAG_LINE_WALKERS) && std::getenv("SGM_B200_LINE_WALKERS") == nullptr;
         e->fused = want_fused && launch_aggregate_fused(a, st, lc);
+        if (!e->fused && e->integer)
+            return fail(e, SGM_ERR_UNSUPPORTED, "integer mode: the image is too wide for a resident sweep and there is no other integer schedule");
         if (!e->fused) launch_aggregate(a, st, lc);
         if (e->fused) cudaMemcpyAsync(e->h_error, e->d_error, sizeof(int), cudaMemcpyDeviceToHost, st);
     } else {
@@ -366,6 +385,7 @@ int check_images(sgm_engine* e, const void* left, size_t ls, const void* right, 
     if (!left || !right) return fail(e, SGM_ERR_INVALID, "left / right image is null");
     if (ls < (size_t)e->p.width || rs < (size_t)e->p.width) return fail(e, SGM_ERR_INVALID, "image stride smaller than width");
     if ((sl && sls < (size_t)e->iw) || (sr && srs < (size_t)e->iw)) return fail(e, SGM_ERR_INVALID, "sky mask stride smaller than width");
+    if (e->integer && (sl || sr)) return fail(e, SGM_ERR_UNSUPPORTED, "integer mode takes no sky masks (their 999999 fill does not fit 16 bits)");
     if (e->busy) return fail(e, SGM_ERR_STATE, "a frame is already in flight on this handle: call sgm_wait first");
     return SGM_OK;
 }
@@ -555,9 +575,9 @@ int sgm_get_tap(sgm_engine* e, int which, int view, void* dst, size_t bytes) {
         case SGM_TAP_BLUR: src = e->p.algo == SGM_ALGO_BM_SAD ? nullptr : e->d_blur + (size_t)view * e->n; break;
         case SGM_TAP_COST:
             // SGM mode: acc/cost buffers are scratch but the filtered cost volume itself is never overwritten
-            src = view < e->views ? e->d_cost + (size_t)view * e->N : nullptr;
+            src = view < e->views ? e->d_cost + (size_t)view * e->vol_words : nullptr;
             break;
-        case SGM_TAP_PATHSUM: src = (e->d_pathsum && view < e->views) ? e->d_pathsum + (size_t)view * e->N : nullptr; break;
+        case SGM_TAP_PATHSUM: src = (e->d_pathsum && view < e->views) ? e->d_pathsum + (size_t)view * e->vol_words : nullptr; break;
         case SGM_TAP_DISP: src = view < e->views ? e->d_disp + (size_t)view * e->n : nullptr; break;
         case SGM_TAP_SUBPIXEL: src = view < e->views ? e->d_sub + (size_t)view * e->n : nullptr; break;
         case SGM_TAP_LR: src = view == 0 ? e->d_lr : nullptr; break;
@@ -566,6 +586,14 @@ int sgm_get_tap(sgm_engine* e, int which, int view, void* dst, size_t bytes) {
         default: break;
     }
     if (!src) return fail(e, SGM_ERR_STATE, "tap %d / view %d is not available in this mode", which, view);
+    if (e->integer && (which == SGM_TAP_COST || which == SGM_TAP_PATHSUM)) {
+        // integer mode: the volume holds 16-bit values; the tap keeps its float layout (every value is exact in float32)
+        CU_TRY(e, cudaMemcpy(dst, src, bytes / 2, cudaMemcpyDeviceToHost));
+        const uint16_t* in = static_cast<const uint16_t*>(dst);
+        float* out = static_cast<float*>(dst);
+        for (size_t t = e->N; t-- > 0;) out[t] = (float)in[t];
+        return SGM_OK;
+    }
     CU_TRY(e, cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
     return SGM_OK;
 }

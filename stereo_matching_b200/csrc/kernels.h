@@ -41,6 +41,10 @@ void launch_census(const uint8_t* img /*[2][h*w]*/, uint64_t* table /*[2][h*w]*/
 void launch_hamming_hfilter(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r,
                             float* cost, int views, int h, int w, int d, int scale, int win, cudaStream_t st,
                             LaunchCounter& lc);
+// Integer mode: the raw Hamming volume (src/Solver.cpp:143-248 without sky mask or cost filter) as packed s16x2 words,
+// [views][h*w*d/2] 32-bit words.
+void launch_hamming_s16x2(const uint64_t* ct_l, const uint64_t* ct_r, void* cost, int views, int h, int w, int d, int scale,
+                          cudaStream_t st, LaunchCounter& lc);
 // src/Solver.cpp:333-368 in place on `views` volumes.
 void launch_vfilter(float* cost, int views, int h, int w, int d, int win, cudaStream_t st, LaunchCounter& lc);
 // src/cost.cpp:4-30 (SAD) for every (pixel, d) of `views` views (view 1 = right view by symmetry).
@@ -58,6 +62,7 @@ struct AggregateArgs {
     int views, h, w, d, paths;
     float P1, P2, unique_ratio;
     int min_gap;        // 1 for SGM (src/SGM.cpp:409), 2 for BM (src/BM.cpp:82)
+    int packed16 = 0;   // integer mode: cost / acc_a / acc_b / pathsum hold s16x2 words (two disparities per 32-bit word), fused schedule only
     // scratch of the fused schedule (sweep_kernels.cu); nullptr -> line walkers only
     float* halo = nullptr;          // fused_halo_bytes() bytes, zeroed once at allocation
     unsigned* launch_seq = nullptr; // HOST counter of sweep launches that used `halo` (tags of the halo payload)

@@ -186,4 +186,160 @@ __device__ __forceinline__ void wta_pixel(const float (&S)[LaneLayout<D>::E], in
     wta_finish<D>(p, ratio, min_gap, parabola, disp_out, sub_out);
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Arithmetic of the aggregation kernels as a policy, so that the schedule (rings, row barrier, halo exchange) is written
+// once.  A pixel's vector is DW 32-bit words spread over the warp as LaneLayout<DW> says; the kernels move the words as
+// `float` registers and never look inside them.
+//
+// F32Arith<D>: the reference's arithmetic.  One word = one float32 cost; parity with src/SGM.cpp is bit for bit.
+template <int D>
+struct F32Arith {
+    static constexpr int DW = D, DISP = D, E = LaneLayout<D>::E;
+    __device__ static __forceinline__ float vmin(const float (&v)[E]) {
+        float m = v[0];
+#pragma unroll
+        for (int k = 1; k < E; ++k) m = fminf(m, v[k]);
+        return warp_min_f32(m);
+    }
+    __device__ static __forceinline__ void step(float (&L)[E], const float (&C)[E], float& m, int lane, float P1, float P2) {
+        path_step<D>(L, C, m, lane, P1, P2);
+    }
+    template <int N>
+    __device__ static __forceinline__ void step_n(float (&L)[N][E], const float (&C)[E], float (&m)[N], int lane, float P1, float P2) {
+        path_step_n<D, N>(L, C, m, lane, P1, P2);
+    }
+    __device__ static __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+    __device__ static __forceinline__ WtaPick reduce(const float (&S)[E], int lane) { return wta_reduce<D>(S, lane); }
+};
+
+// S16x2Arith<DW>: the integer mode of SURVEY 8(f) N4 / north_star ("min-plus recurrences use DPX").  With the cost box
+// filter switched off (window 1x1) and no sky mask every value on the reference's path is a small non-negative integer
+// (Hamming cost <= 62, L <= C + P2, S <= 8 (62 + P2)) that float32 represents exactly, so the SAME recurrence in 16-bit
+// integers gives the SAME numbers.  One word = two disparities {d = 2k (low half), d = 2k + 1 (high half)} as s16x2, and
+//     L' = min(L[d], min(L[d-1], L[d+1], m + P2 - P1) + P1) - m + C
+// is VIMNMX3.S16x2 + VIADDMNMX.S16x2 + IADD3 per word (plus two PRMTs that line the d-1 / d+1 neighbours up); the
+// per-half results never leave [0, 2^15), so the 32-bit add / subtract on packed words is exact.  The penalties arrive
+// as packed words: P1 = {P1, P1}, P2 = {P2 - P1, P2 - P1} (the engine requires 0 <= P1 <= P2); the running minimum m
+// is carried as {m, m}.
+template <int DW_>
+struct S16x2Arith {
+    static constexpr int DW = DW_, DISP = 2 * DW_;
+    using LL = LaneLayout<DW_>;
+    static constexpr int E = LL::E, CW = LL::CW, NCH = LL::NCH;
+    __device__ static __forceinline__ unsigned u(float x) { return __float_as_uint(x); }
+    __device__ static __forceinline__ float f(unsigned x) { return __uint_as_float(x); }
+    __device__ static __forceinline__ unsigned half_min(unsigned packed) {  // min of the two halves, in the low half
+        return __vmins2(packed, packed >> 16) & 0xffffu;
+    }
+    __device__ static __forceinline__ float vmin(const float (&v)[E]) {
+        unsigned m = u(v[0]);
+#pragma unroll
+        for (int k = 1; k < E; ++k) m = __vmins2(m, u(v[k]));
+        return f(__reduce_min_sync(FULL_MASK, half_min(m)) * 0x10001u);
+    }
+    template <int N>
+    __device__ static __forceinline__ void step_n(float (&L)[N][E], const float (&C)[E], float (&m)[N], int lane, float P1f, float P2f) {
+        const unsigned P1 = u(P1f), P2mP1 = u(P2f);
+        unsigned up[N][NCH], dn[N][NCH];
+#pragma unroll
+        for (int n = 0; n < N; ++n)
+#pragma unroll
+            for (int q = 0; q < NCH; ++q) {
+                up[n][q] = __shfl_sync(FULL_MASK, u(L[n][q * CW + CW - 1]), (lane + 31) & 31);  // last word of lane-1 (rotated)
+                dn[n][q] = __shfl_sync(FULL_MASK, u(L[n][q * CW]), (lane + 1) & 31);            // first word of lane+1 (rotated)
+            }
+        unsigned lm[N];
+#pragma unroll
+        for (int n = 0; n < N; ++n) {
+            const unsigned mm = u(m[n]), thr = mm + P2mP1;
+            unsigned nL[E];
+#pragma unroll
+            for (int q = 0; q < NCH; ++q) {
+#pragma unroll
+                for (int e = 0; e < CW; ++e) {
+                    const int k = q * CW + e;
+                    const unsigned cur = u(L[n][k]);
+                    unsigned prev, next;  // the words holding d-1 of the low half / d+1 of the high half
+                    if (e > 0)
+                        prev = u(L[n][k - 1]);
+                    else
+                        prev = lane > 0 ? up[n][q] : (q > 0 ? up[n][q > 0 ? q - 1 : 0] : cur << 16);  // d = 0: the element itself (src/SGM.cpp:96)
+                    if (e < CW - 1)
+                        next = u(L[n][k + 1]);
+                    else
+                        next = lane < 31 ? dn[n][q] : (q < NCH - 1 ? dn[n][q < NCH - 1 ? q + 1 : q] : cur >> 16);  // d = D-1 (:97)
+                    const unsigned dm = __byte_perm(prev, cur, 0x5432);  // {L[d-1] of the low half, of the high half}
+                    const unsigned dp = __byte_perm(cur, next, 0x5432);  // {L[d+1] ...}
+                    const unsigned x = __vimin3_s16x2(dm, dp, thr);
+                    const unsigned t = __viaddmin_s16x2(x, P1, cur);
+                    nL[k] = t - mm + u(C[k]);
+                }
+            }
+            lm[n] = nL[0];
+#pragma unroll
+            for (int k = 0; k < E; ++k) {
+                L[n][k] = f(nL[k]);
+                lm[n] = __vmins2(lm[n], nL[k]);
+            }
+            lm[n] = half_min(lm[n]);
+        }
+#pragma unroll
+        for (int n = 0; n < N; ++n) m[n] = f(__reduce_min_sync(FULL_MASK, lm[n]) * 0x10001u);
+    }
+    __device__ static __forceinline__ void step(float (&L)[E], const float (&C)[E], float& m, int lane, float P1, float P2) {
+        float Ln[1][E], mn[1] = {m};
+#pragma unroll
+        for (int k = 0; k < E; ++k) Ln[0][k] = L[k];
+        step_n<1>(Ln, C, mn, lane, P1, P2);
+#pragma unroll
+        for (int k = 0; k < E; ++k) L[k] = Ln[0][k];
+        m = mn[0];
+    }
+    __device__ static __forceinline__ float add(float a, float b) { return f(u(a) + u(b)); }
+    // Same selection as wta_reduce on the integer sums; the six numbers it returns are exact in float32, and wta_finish
+    // then does the reference's float division / parabola on them unchanged.  A sum (< 2^15) and its disparity (< 2^8)
+    // fit one 32-bit key (S << 8 | d), so "smallest value, first occurrence" is ONE warp-wide integer min (CREDUX.MIN),
+    // and the second distinct value is the same min over the keys whose value differs from the first.
+    __device__ static __forceinline__ WtaPick reduce(const float (&S)[E], int lane) {
+        static_assert(DISP <= 256, "the key holds 8 bits of disparity");
+        constexpr unsigned NONE = 0x7fffffffu;
+        unsigned key[2 * E];
+#pragma unroll
+        for (int k = 0; k < E; ++k) {
+            const unsigned w = u(S[k]), d0 = 2u * LL::disparity(lane, k);
+            key[2 * k] = ((w << 8) & 0xffff00u) | d0;
+            key[2 * k + 1] = ((w >> 8) & 0xffff00u) | (d0 + 1u);
+        }
+        unsigned lk = key[0];
+#pragma unroll
+        for (int k = 1; k < 2 * E; ++k) lk = min(lk, key[k]);
+        const unsigned g1 = __reduce_min_sync(FULL_MASK, lk);
+        const unsigned min_d = g1 & 0xffu, above = (g1 | 0xffu) + 1u;  // keys >= above hold a value different from the minimum
+        unsigned ls = NONE;
+#pragma unroll
+        for (int k = 0; k < 2 * E; ++k) ls = min(ls, key[k] >= above ? key[k] : NONE);
+        const unsigned g2 = __reduce_min_sync(FULL_MASK, ls);
+        unsigned nb = 0;  // {S[min_d - 1], S[min_d + 1]} as low / high half; zero in the lanes that do not own them
+#pragma unroll
+        for (int k = 0; k < E; ++k) {
+            const unsigned w = u(S[k]);
+            const int r = (int)min_d - (int)(2u * LL::disparity(lane, k));  // distance of the winner from this word's low half
+            if (r == 1) nb |= w & 0xffffu;          // low half is d - 1
+            if (r == 2) nb |= w >> 16;              // high half is d - 1
+            if (r == 0) nb |= w & 0xffff0000u;      // high half is d + 1
+            if (r == -1) nb |= w << 16;             // low half is d + 1
+        }
+        nb = __reduce_or_sync(FULL_MASK, nb);
+        WtaPick p;
+        p.c0 = (float)(g1 >> 8);
+        p.sec = g2 == NONE ? INFINITY : (float)(g2 >> 8);
+        p.min_d = (int)min_d;
+        p.sec_d = (int)(g2 & 0xffu);
+        p.cm = (float)(nb & 0xffffu);
+        p.cp = (float)(nb >> 16);
+        return p;
+    }
+};
+
 }  // namespace sgmb200

@@ -20,6 +20,7 @@
 // cooperatively so that every block is resident, and every wait has a time-out that raises an error flag instead of
 // hanging.
 #include <cstdlib>
+#include <cstring>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -285,7 +286,7 @@ __device__ __forceinline__ void cp_async_lane(unsigned dst, const void* src) {
         asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
 }
 
-template <int D, int PF, int WARPS>
+template <int D, int PF, int WARPS, class AR>
 __global__ void __launch_bounds__(WARPS * 32) sgm_hpair_async_kernel(const float* __restrict__ cost, float* __restrict__ out_fwd,
                                                                      float* __restrict__ out_bwd, int h, int w, float P1,
                                                                      float P2, size_t vol_stride) {
@@ -327,9 +328,9 @@ __global__ void __launch_bounds__(WARPS * 32) sgm_hpair_async_kernel(const float
                 if (s == 0) {
 #pragma unroll
                     for (int k = 0; k < E; ++k) L[k] = C[k];
-                    m = warp_min_f32(vec_min<E>(L));
+                    m = AR::vmin(L);
                 } else {
-                    path_step<D>(L, C, m, lane, P1, P2);
+                    AR::step(L, C, m, lane, P1, P2);
                 }
                 stg_vec<D>(po, L);
                 po += step;
@@ -356,7 +357,7 @@ __global__ void __launch_bounds__(WARPS * 32) sgm_hpair_async_kernel(const float
 // unrolled body and every shared-memory address is base + immediate.
 constexpr int SWEEP_DOWN = 0, SWEEP_UP = 1, SWEEP_UP_KEEP = 2;
 
-template <int D, int NW, int MODE, int PATHS, int PF, int MINB>
+template <int D, int NW, int MODE, int PATHS, int PF, int MINB, class AR>
 __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArgs a) {
     constexpr bool UP = MODE != SWEEP_DOWN, KEEP_S = MODE == SWEEP_UP_KEEP;  // KEEP_S: also write the path sum S (debug tap)
     using LL = LaneLayout<D>;
@@ -481,7 +482,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                 if (r == 0) {
 #pragma unroll
                     for (int k = 0; k < E; ++k) F[k] = V[k] = G[k] = C[k];
-                    mV = warp_min_f32(vec_min<E>(V));
+                    mV = AR::vmin(V);
                     if (DIAG) {
                         if (f_pub) HIO::publish(f_pub, lane, F, tag);
                         sts_pixel<D>(f_dst + par * PAR_BYTES, F);
@@ -492,7 +493,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                         }
                     }
                 } else if (!DIAG) {
-                    path_step<D>(V, C, mV, lane, a.P1, a.P2);
+                    AR::step(V, C, mV, lane, a.P1, a.P2);
                 } else {
                     float P[3][E], mP[3];
                     // previous-row vectors: F and (unless it comes from another block) G from shared memory
@@ -505,17 +506,17 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                     if (!g_global) {
                         lds_pixel<D>(g_src + (par ^ 1u) * PAR_BYTES, P[2]);
                         mP[2] = lds_f32(gm_src + (par ^ 1u) * MIN_PAR_BYTES);
-                        path_step_n<D, 3>(P, C, mP, lane, a.P1, a.P2);
+                        AR::template step_n<3>(P, C, mP, lane, a.P1, a.P2);
                     } else {
                         // block-edge warp: F first (a neighbouring block is waiting for it), then V and G together
                         float P0[1][E], m0[1] = {mP[0]};
 #pragma unroll
                         for (int k = 0; k < E; ++k) P0[0][k] = P[0][k];
-                        path_step_n<D, 1>(P0, C, m0, lane, a.P1, a.P2);
+                        AR::template step_n<1>(P0, C, m0, lane, a.P1, a.P2);
                         if (f_init) {
 #pragma unroll
                             for (int k = 0; k < E; ++k) P0[0][k] = C[k];
-                            m0[0] = warp_min_f32(vec_min<E>(C));
+                            m0[0] = AR::vmin(C);
                         }
                         if (f_pub) HIO::publish(f_pub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, P0[0], tag);
                         float P12[2][E], m12[2];
@@ -529,8 +530,8 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
 #pragma unroll
                         for (int k = 0; k < E; ++k) P12[0][k] = V[k];
                         m12[0] = mV;
-                        m12[1] = warp_min_f32(vec_min<E>(P12[1]));
-                        path_step_n<D, 2>(P12, C, m12, lane, a.P1, a.P2);
+                        m12[1] = AR::vmin(P12[1]);
+                        AR::template step_n<2>(P12, C, m12, lane, a.P1, a.P2);
 #pragma unroll
                         for (int k = 0; k < E; ++k) {
                             P[0][k] = P0[0][k];
@@ -545,12 +546,12 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                         if (f_init) {
 #pragma unroll
                             for (int k = 0; k < E; ++k) P[0][k] = C[k];
-                            mP[0] = warp_min_f32(vec_min<E>(C));
+                            mP[0] = AR::vmin(C);
                         }
                         if (g_init) {
 #pragma unroll
                             for (int k = 0; k < E; ++k) P[2][k] = C[k];
-                            mP[2] = warp_min_f32(vec_min<E>(C));
+                            mP[2] = AR::vmin(C);
                         }
                     }  // (f_pub != nullptr implies g_global, handled above)
 #pragma unroll
@@ -580,12 +581,12 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                 if (!UP) {
                     float A[E];
 #pragma unroll
-                    for (int k = 0; k < E; ++k) A[k] = __fadd_rn(__fadd_rn(X[k], Y[k]), V[k]);  // (L1 + L2) + L3
+                    for (int k = 0; k < E; ++k) A[k] = AR::add(AR::add(X[k], Y[k]), V[k]);  // (L1 + L2) + L3
                     stg_vec<D>(oa, A);
                     if (DIAG) {
                         float B[E];
 #pragma unroll
-                        for (int k = 0; k < E; ++k) B[k] = __fadd_rn(F[k], G[k]);  // L5 + L6 (float add commutes)
+                        for (int k = 0; k < E; ++k) B[k] = AR::add(F[k], G[k]);  // L5 + L6 (float add commutes)
                         stg_vec<D>(ob, B);
                         ob += rstep;
                     }
@@ -594,15 +595,15 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                     float S[E];
                     if (!DIAG) {
 #pragma unroll
-                        for (int k = 0; k < E; ++k) S[k] = __fadd_rn(X[k], V[k]);
+                        for (int k = 0; k < E; ++k) S[k] = AR::add(X[k], V[k]);
                     } else if (!swap) {
 #pragma unroll
                         for (int k = 0; k < E; ++k)  // (A + L4) + ((B + L7) + L8), src/SGM.cpp:386-390
-                            S[k] = __fadd_rn(__fadd_rn(X[k], V[k]), __fadd_rn(__fadd_rn(Y[k], F[k]), G[k]));
+                            S[k] = AR::add(AR::add(X[k], V[k]), AR::add(AR::add(Y[k], F[k]), G[k]));
                     } else {
 #pragma unroll
                         for (int k = 0; k < E; ++k)
-                            S[k] = __fadd_rn(__fadd_rn(X[k], V[k]), __fadd_rn(__fadd_rn(Y[k], G[k]), F[k]));
+                            S[k] = AR::add(AR::add(X[k], V[k]), AR::add(AR::add(Y[k], G[k]), F[k]));
                     }
                     if (KEEP_S) {
                         stg_vec<D>(os, S);
@@ -610,14 +611,14 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                     }
                     // the warp-wide half of the selection now; the scalar half (uniqueness division, parabola, stores)
                     // once per 32 rows with one lane per row instead of 32 lanes repeating the same arithmetic
-                    const WtaPick pk = wta_reduce<D>(S, lane);
+                    const WtaPick pk = AR::reduce(S, lane);
                     if (lane == (r & 31)) stash = pk;
                     if ((r & 31) == 31 || r == h - 1) {
                         const int rr = (r & ~31) + lane;
                         if (rr <= r) {
                             int dd;
                             float sub;
-                            wta_finish<D>(stash, a.ratio, a.min_gap, true, dd, sub);
+                            wta_finish<AR::DISP>(stash, a.ratio, a.min_gap, true, dd, sub);
                             const size_t o = opix0 + (ptrdiff_t)rr * pstep;
                             a.disp[o] = (uint16_t)dd;
                             a.subpixel[o] = sub;
@@ -644,9 +645,9 @@ constexpr size_t sweep_ring_bytes() {
     return (size_t)CFG::NW * CFG::PF * 3 * D * sizeof(float);
 }
 
-template <int D, int MODE, int PATHS, class CFG>
+template <int D, int MODE, int PATHS, class CFG, class AR>
 cudaError_t launch_sweep(const SweepArgs& sa, int nblk, int views, bool cooperative, cudaStream_t st) {
-    auto kern = sgm_sweep_kernel<D, CFG::NW, MODE, PATHS, CFG::PF, CFG::MINB>;
+    auto kern = sgm_sweep_kernel<D, CFG::NW, MODE, PATHS, CFG::PF, CFG::MINB, AR>;
     constexpr size_t ring_bytes = sweep_ring_bytes<D, CFG>();
     cudaError_t attr = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes);  // per device: cheap, so always
     if (attr != cudaSuccess) return attr;
@@ -658,7 +659,7 @@ cudaError_t launch_sweep(const SweepArgs& sa, int nblk, int views, bool cooperat
     return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(nblk, views), dim3(CFG::NW * 32), params, ring_bytes, st);
 }
 
-template <int D, int PATHS, class CFG>
+template <int D, int PATHS, class CFG, class AR>
 int sweep_capacity(int device) {
     static int cached[16] = {};  // per device; the answer only depends on the kernel and the device
     if (device >= 0 && device < 16 && cached[device]) return cached[device] - 1;
@@ -670,36 +671,39 @@ int sweep_capacity(int device) {
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<D, CFG>());
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&out, kern, CFG::NW * 32, sweep_ring_bytes<D, CFG>());
     };
-    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_DOWN, PATHS, CFG::PF, CFG::MINB>, per_sm[0]);
-    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP, PATHS, CFG::PF, CFG::MINB>, per_sm[1]);
-    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP_KEEP, PATHS, CFG::PF, CFG::MINB>, per_sm[2]);
+    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_DOWN, PATHS, CFG::PF, CFG::MINB, AR>, per_sm[0]);
+    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP, PATHS, CFG::PF, CFG::MINB, AR>, per_sm[1]);
+    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP_KEEP, PATHS, CFG::PF, CFG::MINB, AR>, per_sm[2]);
     const int least = per_sm[0] < per_sm[1] ? (per_sm[0] < per_sm[2] ? per_sm[0] : per_sm[2]) : (per_sm[1] < per_sm[2] ? per_sm[1] : per_sm[2]);
     const int cap = coop ? sms * least : 0;
     if (device >= 0 && device < 16) cached[device] = cap + 1;
     return cap;
 }
 
-template <int D, int PATHS, class CFG>
+// D = 32-bit words per pixel: the number of disparities for F32Arith, half of it for S16x2Arith (a.d stays the number
+// of disparities).
+template <int D, int PATHS, class CFG, class AR = F32Arith<D>>
 bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
+    constexpr bool PACKED = AR::DISP != D;
     const int nblk = (a.w + CFG::NW - 1) / CFG::NW;
     int views_per_launch = a.views;
     if (PATHS == 8) {
         int device = 0;
         cudaGetDevice(&device);
-        const int cap = sweep_capacity<D, PATHS, CFG>(device);
+        const int cap = sweep_capacity<D, PATHS, CFG, AR>(device);
         static const bool split = std::getenv("SGM_B200_SWEEP_SPLIT_VIEWS") != nullptr;
         if (nblk * a.views > cap || split) views_per_launch = 1;
         if (nblk > cap) return false;  // image too wide for a resident row-synchronous sweep: caller falls back to line walkers
     }
-    const size_t vol = (size_t)a.h * a.w * a.d;
+    const size_t vol = (size_t)a.h * a.w * D;
     {
         constexpr int PFH = (LaneLayout<D>::E >= 8) ? 8 : 16, HW = 4;
         constexpr size_t ring_bytes = (size_t)HW * PFH * D * sizeof(float);  // 32 KB for D >= 128
         static const bool legacy = std::getenv("SGM_B200_HPAIR_LEGACY") != nullptr;
-        if (legacy)
+        if (legacy && !PACKED)
             sgm_hpair_kernel<D, PFH><<<dim3((a.h + 3) / 4, a.views, 2), 128, 0, st>>>(a.cost, a.acc_a, a.acc_b, a.h, a.w, a.P1, a.P2, vol);
         else
-            sgm_hpair_async_kernel<D, PFH, HW><<<dim3((a.h + HW - 1) / HW, a.views, 2), HW * 32, ring_bytes, st>>>(
+            sgm_hpair_async_kernel<D, PFH, HW, AR><<<dim3((a.h + HW - 1) / HW, a.views, 2), HW * 32, ring_bytes, st>>>(
                 a.cost, a.acc_a, a.acc_b, a.h, a.w, a.P1, a.P2, vol);
         lc.note("sgm_hpair_kernel");
     }
@@ -734,9 +738,9 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
         sa.tag_base = ++(*a.launch_seq) << 12;
         for (int v0 = 0; v0 < a.views; v0 += views_per_launch) {
             sa.view0 = v0;
-            cudaError_t e = !up         ? launch_sweep<D, SWEEP_DOWN, PATHS, CFG>(sa, nblk, views_per_launch, PATHS == 8, st)
-                            : a.pathsum ? launch_sweep<D, SWEEP_UP_KEEP, PATHS, CFG>(sa, nblk, views_per_launch, PATHS == 8, st)
-                                        : launch_sweep<D, SWEEP_UP, PATHS, CFG>(sa, nblk, views_per_launch, PATHS == 8, st);
+            cudaError_t e = !up         ? launch_sweep<D, SWEEP_DOWN, PATHS, CFG, AR>(sa, nblk, views_per_launch, PATHS == 8, st)
+                            : a.pathsum ? launch_sweep<D, SWEEP_UP_KEEP, PATHS, CFG, AR>(sa, nblk, views_per_launch, PATHS == 8, st)
+                                        : launch_sweep<D, SWEEP_UP, PATHS, CFG, AR>(sa, nblk, views_per_launch, PATHS == 8, st);
             if (e != cudaSuccess && lc.err == cudaSuccess) {
                 lc.err = e;
                 lc.failed = "sgm_sweep_kernel (launch)";
@@ -797,6 +801,40 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
     return fused_impl<D, 8, typename DefaultCfg<D>::type>(a, st, lc);
 }
 
+// Integer mode (S16x2Arith): DW = a.d / 2 words per pixel; the penalties travel as packed s16x2 bit patterns.
+template <int DW>
+bool fused_dispatch_packed(const AggregateArgs& a0, cudaStream_t st, LaunchCounter& lc) {
+    AggregateArgs a = a0;
+    const unsigned p1 = (unsigned)a0.P1, p2m = (unsigned)(a0.P2 - a0.P1);
+    const unsigned P1w = p1 * 0x10001u, P2w = p2m * 0x10001u;
+    static_assert(sizeof(float) == sizeof(unsigned), "carrier");
+    memcpy(&a.P1, &P1w, sizeof(float));
+    memcpy(&a.P2, &P2w, sizeof(float));
+    using AR = S16x2Arith<DW>;
+    if (a.paths != 8) return fused_impl<DW, 4, typename DefaultCfg<DW>::type, AR>(a, st, lc);
+    static const int cfg = [] {
+        const char* e = std::getenv("SGM_B200_ISWEEP_CFG");
+        return e ? std::atoi(e) : 0;
+    }();
+    switch (cfg) {
+        case 1: return fused_impl<DW, 8, SweepCfg<10, 4, 2>, AR>(a, st, lc);
+        case 2: return fused_impl<DW, 8, SweepCfg<8, 4, 3>, AR>(a, st, lc);
+        case 3: return fused_impl<DW, 8, SweepCfg<19, 4, 1>, AR>(a, st, lc);
+        case 4: return fused_impl<DW, 8, SweepCfg<19, 6, 1>, AR>(a, st, lc);
+        case 5: return fused_impl<DW, 8, SweepCfg<17, 4, 1>, AR>(a, st, lc);
+        case 6: return fused_impl<DW, 8, SweepCfg<9, 4, 2>, AR>(a, st, lc);
+        default: break;
+    }
+    int device = 0, sms = 0;
+    cudaGetDevice(&device);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    using Wide = SweepCfg<19, 4, 1>;
+    using Def = typename DefaultCfg<DW>::type;
+    const int wide_blocks = a.views * ((a.w + Wide::NW - 1) / Wide::NW), def_blocks = a.views * ((a.w + Def::NW - 1) / Def::NW);
+    if (DW <= 128 && def_blocks > sms && wide_blocks <= sms - 12) return fused_impl<DW, 8, Wide, AR>(a, st, lc);
+    return fused_impl<DW, 8, Def, AR>(a, st, lc);
+}
+
 }  // namespace
 
 size_t fused_halo_bytes(int views, int w, int d) {
@@ -806,6 +844,14 @@ size_t fused_halo_bytes(int views, int w, int d) {
 
 bool launch_aggregate_fused(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
     if (!a.halo || !a.launch_seq || !a.error || !a.acc_b || a.h > 4000) return false;
+    if (a.packed16) {
+        switch (a.d) {
+            case 64: return fused_dispatch_packed<32>(a, st, lc);
+            case 128: return fused_dispatch_packed<64>(a, st, lc);
+            case 256: return fused_dispatch_packed<128>(a, st, lc);
+            default: return false;
+        }
+    }
     switch (a.d) {
         case 32: return fused_dispatch<32>(a, st, lc);
         case 64: return fused_dispatch<64>(a, st, lc);

@@ -17,12 +17,27 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from stereo_matching_b200 import capi, stream, synth  # noqa: E402
 
+def _variant(**kw):
+    """SGM with extra sgm_params / flags (e.g. the integer mode), as a class-like factory."""
+    def make(h, w, s, d, flags=0):
+        over = dict(kw)
+        return capi.SGM(h, w, s, d, flags=flags | over.pop("flags", 0), **over)
+    return make
+
+
 CONFIGS = [
     ("configs[0] KITTI 1242x375 census + 8-path SGM D=64", capi.SGM, 375, 1242, 64, dict(bg=12, fg=40)),
     ("configs[1] KITTI 1242x375 SAD 9x9 block matching D=64 + LR-check", capi.BMSad, 375, 1242, 64, dict(bg=12, fg=40)),
     ("configs[1b] KITTI 1242x375 reference BM (census) D=64", capi.BM, 375, 1242, 64, dict(bg=12, fg=40)),
     ("configs[2] KITTI 1242x375 census + 8-path SGM D=128", capi.SGM, 375, 1242, 128, dict(bg=12, fg=40)),
     ("configs[3] 1920x1080 8-path SGM D=256", capi.SGM, 1080, 1920, 256, dict(bg=24, fg=200)),
+    # the same SGM with the cost filter off (window 1x1): float arithmetic vs the integer / DPX mode (identical results)
+    ("configs[2] no cost filter, float32 volumes D=128", _variant(box_w=1, box_h=1), 375, 1242, 128, dict(bg=12, fg=40)),
+    ("configs[2] no cost filter, INTEGER mode (s16x2, DPX) D=128", _variant(box_w=1, box_h=1, flags=capi.FLAG_INTEGER), 375, 1242, 128,
+     dict(bg=12, fg=40)),
+    ("configs[0] no cost filter, INTEGER mode D=64", _variant(box_w=1, box_h=1, flags=capi.FLAG_INTEGER), 375, 1242, 64, dict(bg=12, fg=40)),
+    ("configs[3] no cost filter, INTEGER mode 1920x1080 D=256", _variant(box_w=1, box_h=1, flags=capi.FLAG_INTEGER), 1080, 1920, 256,
+     dict(bg=24, fg=200)),
 ]
 
 
@@ -55,7 +70,10 @@ def run(name, cls, h, w, d, gen, frames):
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--frames", type=int, default=60)
+    ap.add_argument("--only", default="", help="substring of the config names to run")
     args = ap.parse_args()
     for cfg in CONFIGS:
+        if args.only not in cfg[0]:
+            continue
         n = args.frames if cfg[2] * cfg[3] * cfg[4] < 3e8 else max(6, args.frames // 10)
         print(json.dumps(run(*cfg, frames=n)), flush=True)

@@ -111,6 +111,23 @@ def test_sad_volume_against_reference_function():
     assert bits_equal(want, got)
 
 
+@pytest.mark.parametrize("h,w,d,scale,paths,noise", [(48, 96, 64, 1, 8, 20), (40, 150, 128, 1, 8, 50), (33, 70, 64, 1, 4, 30),
+                                                      (60, 120, 64, 2, 8, 15)])
+def test_integer_restatement_equals_float_restatement_without_cost_filter(h, w, d, scale, paths, noise):
+    # the engine's integer / DPX mode (SGM_FLAG_INTEGER): with the cost filter window at 1x1 every number on the
+    # reference's float path is a small integer, so a 16-bit integer restatement of the same loops must reproduce the
+    # float restatement (which is pinned against the reference) exactly - that is the oracle of the integer mode
+    L, R, _ = synth.random_dot_pair(h, w, seed=h + w + d, bg=3, fg=min(15, d // 3), noise=noise)
+    out = restate.process(L, R, scale, d, "sgm", taps=restate.ALL_TAPS, box_w=scale, box_h=scale, paths=paths)
+    for v in (0, 1):
+        raw, hv, S = out["cost_raw"][v], out["cost_hv"][v], out["S"][v]
+        assert bits_equal(raw, hv)                                    # window 1: the filters are the identity
+        assert raw.min() >= 0 and raw.max() <= 62 and np.array_equal(raw, np.floor(raw))
+        assert S.max() <= paths * (62 + 100) and np.array_equal(S, np.floor(S))
+        Si = restate.aggregate_u16(raw.astype(np.uint16), 10, 100, paths)
+        assert np.array_equal(Si.astype(np.float32), S)
+
+
 def test_widened_restatement_runs_d256():
     # D=256 cannot run through the reference (src/Solver.cpp:10 asserts); the restatement is the oracle there
     L, R, _ = synth.random_dot_pair(48, 400, seed=4, bg=24, fg=200, noise=4)

@@ -21,9 +21,9 @@ pytestmark = pytest.mark.gpu
 H = restate.fnv1a64
 
 
-def _check_sgm_against_restatement(L, R, scale, d, sl=None, sr=None, paths=8, flags=0):
-    want = restate.process(L, R, scale, d, "sgm", sl, sr, taps=restate.ALL_TAPS, paths=paths)
-    sv = capi.SGM(L.shape[0], L.shape[1], scale, d, flags=capi.FLAG_KEEP_VOLUMES | flags, paths=paths)
+def _check_sgm_against_restatement(L, R, scale, d, sl=None, sr=None, paths=8, flags=0, **over):
+    want = restate.process(L, R, scale, d, "sgm", sl, sr, taps=restate.ALL_TAPS, paths=paths, **over)
+    sv = capi.SGM(L.shape[0], L.shape[1], scale, d, flags=capi.FLAG_KEEP_VOLUMES | flags, paths=paths, **over)
     sv.process(L, R, sl, sr)
     bad = {}
     for v in (0, 1):
@@ -85,6 +85,66 @@ def test_sgm_halo_tag_sequence_wraps(monkeypatch):
 def test_sgm_four_paths_vs_oracle(flags):
     L, R, _ = synth.random_dot_pair(80, 144, seed=21, bg=4, fg=13, noise=10)
     _check_sgm_against_restatement(L, R, 1, 64, paths=4, flags=flags)
+
+
+# ---- integer / DPX mode (SGM_FLAG_INTEGER) ----------------------------------------------------------
+# Oracle: the restatement with the cost filter window at 1x1 (pinned against the reference for the default window, and
+# against its own 16-bit integer form in tests/test_oracle_cpu.py).  Every tap is compared bit for bit, like the float mode.
+@pytest.mark.parametrize("h,w,d,scale,noise", [
+    (96, 160, 64, 1, 6),
+    (64, 300, 128, 1, 25),
+    (97, 161, 128, 1, 60),    # odd sizes, heavy noise
+    (300, 200, 64, 1, 12),    # W < H
+    (72, 250, 256, 1, 10),    # 128 words per pixel
+    (200, 320, 64, 2, 10),    # scale 2 (box window 2 / 2 = 1)
+    (16, 16, 64, 1, 20), (16, 161, 128, 1, 25), (40, 21, 128, 1, 25), (19, 75, 64, 1, 25), (24, 48, 256, 1, 25),
+])
+def test_integer_mode_stages_bit_exact_vs_oracle(h, w, d, scale, noise):
+    L, R, _ = synth.random_dot_pair(h, w, seed=h * 5 + d, bg=3, fg=max(4, min(17, d // 2, w // 3)), noise=noise)
+    _check_sgm_against_restatement(L, R, scale, d, flags=capi.FLAG_INTEGER, box_w=scale, box_h=scale)
+
+
+def test_integer_mode_four_paths_and_other_penalties():
+    L, R, _ = synth.random_dot_pair(80, 144, seed=21, bg=4, fg=13, noise=10)
+    _check_sgm_against_restatement(L, R, 1, 64, paths=4, flags=capi.FLAG_INTEGER, box_w=1, box_h=1)
+    _check_sgm_against_restatement(L, R, 1, 128, flags=capi.FLAG_INTEGER, box_w=1, box_h=1, P1=7, P2=300)
+    _check_sgm_against_restatement(L, R, 1, 64, flags=capi.FLAG_INTEGER, box_w=1, box_h=1, P1=0, P2=0)
+
+
+def test_integer_mode_equals_float_mode_at_kitti_size():
+    # BASELINE.json config 2 shape (1242x375, D=128): the float engine with the cost filter off is the reference's
+    # arithmetic; the integer engine must return the same bits for every result
+    h, w, d = 375, 1242, 128
+    L, R, gt = synth.random_dot_pair(h, w, seed=1234, bg=12, fg=40, noise=8)
+    a = capi.SGM(h, w, 1, d, box_w=1, box_h=1)
+    b = capi.SGM(h, w, 1, d, box_w=1, box_h=1, flags=capi.FLAG_INTEGER)
+    a.process(L, R), b.process(L, R)
+    for v in (0, 1):
+        assert bits_equal(a.tap("disp", v), b.tap("disp", v)) and bits_equal(a.tap("subpixel", v), b.tap("subpixel", v))
+    assert bits_equal(a.tap("lr"), b.tap("lr")) and bits_equal(a.get_disp(), b.get_disp())
+    f = b.get_disp()
+    ok = (f <= d - 1) & (np.arange(w)[None, :] >= d)
+    assert ok.mean() > 0.5 and (np.abs(f[ok] - gt[ok]) <= 1).mean() > 0.95
+    assert b.device_bytes < 0.6 * a.device_bytes     # 16-bit volumes
+    for _ in range(2):                                # deterministic, handle reusable
+        assert bits_equal(b.process(L, R).get_disp(), f)
+    a.close(), b.close()
+
+
+def test_integer_mode_rejects_what_it_cannot_represent():
+    for over in (dict(), dict(box_w=1, box_h=1, P2=5000), dict(box_w=1, box_h=1, P1=20, P2=10)):
+        with pytest.raises(capi.SgmError) as e:
+            capi.SGM(64, 64, 1, 64, flags=capi.FLAG_INTEGER, **over)   # default box 5x3 / too large penalties / P1 > P2
+        assert e.value.code == 2
+    with pytest.raises(capi.SgmError) as e:
+        capi.SGM(64, 64, 1, 32, flags=capi.FLAG_INTEGER, box_w=1, box_h=1)
+    assert e.value.code == 2
+    sv = capi.SGM(64, 64, 1, 64, flags=capi.FLAG_INTEGER, box_w=1, box_h=1)
+    z = np.zeros((64, 64), np.uint8)
+    with pytest.raises(capi.SgmError) as e:
+        sv.process(z, z, z, z)                                         # sky masks: 999999 does not fit 16 bits
+    assert e.value.code == 2
+    sv.close()
 
 
 @pytest.mark.parametrize("h,w,d,scale,sky", [(120, 200, 64, 1, True), (64, 300, 128, 1, False), (72, 250, 256, 1, False)])
