@@ -320,24 +320,26 @@ struct S16x2Arith {
 #pragma unroll
         for (int k = 0; k < 2 * E; ++k) ls = min(ls, key[k] >= above ? key[k] : NONE);
         const unsigned g2 = __reduce_min_sync(FULL_MASK, ls);
-        unsigned nb = 0;  // {S[min_d - 1], S[min_d + 1]} as low / high half; zero in the lanes that do not own them
+        // the winner's two neighbours: min_d is warp-uniform, so the word that holds a neighbour is picked by a uniform
+        // index and fetched with one shuffle from the lane that owns it (out-of-range neighbours are never used)
+        auto fetch = [&](unsigned d) -> unsigned {
+            const unsigned widx = (d >> 1) & (unsigned)(DW - 1);             // word of the pixel, wrapped into range
+            const unsigned q = widx / (unsigned)LL::CHUNK_SPAN, in = widx % (unsigned)LL::CHUNK_SPAN;
+            const unsigned k = q * CW + in % CW;                              // register of the owning lane
+            unsigned w = u(S[0]);
 #pragma unroll
-        for (int k = 0; k < E; ++k) {
-            const unsigned w = u(S[k]);
-            const int r = (int)min_d - (int)(2u * LL::disparity(lane, k));  // distance of the winner from this word's low half
-            if (r == 1) nb |= w & 0xffffu;          // low half is d - 1
-            if (r == 2) nb |= w >> 16;              // high half is d - 1
-            if (r == 0) nb |= w & 0xffff0000u;      // high half is d + 1
-            if (r == -1) nb |= w << 16;             // low half is d + 1
-        }
-        nb = __reduce_or_sync(FULL_MASK, nb);
+            for (int e = 1; e < E; ++e) w = k == (unsigned)e ? u(S[e]) : w;
+            w = __shfl_sync(FULL_MASK, w, (int)(in / CW));
+            return (d & 1u) ? w >> 16 : w & 0xffffu;
+        };
+        const unsigned cm_i = fetch(min_d - 1u), cp_i = fetch(min_d + 1u);
         WtaPick p;
         p.c0 = (float)(g1 >> 8);
         p.sec = g2 == NONE ? INFINITY : (float)(g2 >> 8);
         p.min_d = (int)min_d;
         p.sec_d = (int)(g2 & 0xffu);
-        p.cm = (float)(nb & 0xffffu);
-        p.cp = (float)(nb >> 16);
+        p.cm = (float)cm_i;
+        p.cp = (float)cp_i;
         return p;
     }
 };

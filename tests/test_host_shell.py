@@ -75,7 +75,7 @@ def test_division_by_window_size_is_exact():
     assert out.returncode == 0, out.stdout
 
 
-def _run_driver(tmp, algo, h, w, s, d, L, R, sky):
+def _run_driver(tmp, algo, h, w, s, d, L, R, sky, env=None):
     exe = _make("_build/host_shell_main")
     L.tofile(os.path.join(tmp, "l.raw"))
     R.tofile(os.path.join(tmp, "r.raw"))
@@ -86,7 +86,7 @@ def _run_driver(tmp, algo, h, w, s, d, L, R, sky):
         sky[1].tofile(sr)
     prefix = os.path.join(tmp, "out")
     r = subprocess.run([exe, algo, str(h), str(w), str(s), str(d), os.path.join(tmp, "l.raw"), os.path.join(tmp, "r.raw"), sl, sr, prefix],
-                       capture_output=True, text=True)
+                       capture_output=True, text=True, env=dict(os.environ, **(env or {})))
     assert r.returncode == 0, r.stdout + r.stderr
     ih, iw = h // s, w // s
     disp = np.fromfile(prefix + "_disp.f32", np.float32).reshape(ih, iw)
@@ -140,6 +140,18 @@ def test_node_style_driver_matches_oracle(algo, h, w, s, d, sky):
     # get_point_cloud(): node.cpp:119-143 on the device
     want_xyz, _ = restate.point_cloud(want, L, d, s, 718.856, 718.856, 607.1928, 185.2157, 0.5, 100.0)
     assert cloud.shape == want_xyz.shape and np.array_equal(cloud.view(np.uint64), want_xyz.view(np.uint64))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("h,w,s,d", [(96, 192, 1, 64), (120, 200, 2, 64)])
+def test_node_style_driver_integer_mode(h, w, s, d):
+    # SGM_B200_INTEGER=1: the C++ shell opens the engine in its integer / DPX mode (SGM without the cost filter);
+    # oracle = the restatement with the cost filter window at 1x1
+    L, R, _ = synth.random_dot_pair(h, w, seed=h + d, bg=5, fg=min(17, d // 2), noise=15)
+    want = restate.process(L, R, s, d, "sgm", box_w=s, box_h=s)["f_final"]
+    with tempfile.TemporaryDirectory() as tmp:
+        disp, disp2, _, _, _ = _run_driver(tmp, "sgm", h, w, s, d, L, R, None, env={"SGM_B200_INTEGER": "1"})
+    assert bits_equal(disp, want) and bits_equal(disp2, want)
 
 
 def test_cost_h_probes_match_oracle_dense_volumes():
