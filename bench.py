@@ -376,7 +376,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--inflight", type=int, default=3, help="frames in flight per GPU (engine handles)")
+    ap.add_argument("--inflight", type=int, default=5, help="frames in flight per GPU (engine handles)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--mode", default="reference", choices=sorted(MODES), help="secondary lines: nofilter / integer (see MODES)")
     args = ap.parse_args()
