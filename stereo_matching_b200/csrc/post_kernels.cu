@@ -161,20 +161,23 @@ __global__ void __launch_bounds__(1024) median_fill_ring_kernel(const float* __r
 // between two barriers: a hole at (i, c + b), b < B, needs row i-1 final up to column c + b + RW <= c + K - 1, which row
 // i-1 (cursor c + K) finished in earlier batches, and rows below have not touched what it reads (their cursors trail by
 // K, 2K, ...).  Same raster-order result with (W + K*H) / B barriers instead of W + 3*H.
-template <int WH, int WW, int K, int RING, int LEADB>
+template <int WH, int WW, int K, int RING, int LEADB, int COOP_MAX>
 __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __restrict__ src, float* __restrict__ f, int h, int w,
                                                                   int d) {
     constexpr int RH = WH / 2, RW = WW / 2, B = K - RW, NWIN = WH * WW, LOOK = K * RH + RW, AHEAD = LOOK + 1;
     static_assert(B >= 1 && AHEAD + LEADB * B + B + LOOK < RING && (RING & (RING - 1)) == 0, "window does not fit the ring");
-    extern __shared__ float ring[];  // [h][RING]
+    // rows are RS = RING + 1 floats apart: with one row per lane a power-of-two stride would put all 32 lanes of a warp on
+    // the same shared-memory bank (a 32-way conflict on every column check, feed and gather)
+    constexpr int RS = RING + 1;
+    extern __shared__ float ring[];  // [h][RS]
     const float vmax = (float)(d - 1);
     const int i = threadIdx.x;       // one row per thread (h <= blockDim.x)
     const int lane = threadIdx.x & 31;
     static_assert(NWIN <= 32, "the window must fit a warp");
-    constexpr int COOP_MAX = 2;      // up to this many holes per warp and column are filled one after the other by the whole warp
+    // COOP_MAX: up to this many holes per warp and column are filled one after the other by the whole warp
     const bool row_ok = i < h;
     const bool interior_row = i >= RH && i < h - RH;
-    float* myring = ring + (size_t)(row_ok ? i : 0) * RING;
+    float* myring = ring + (size_t)(row_ok ? i : 0) * RS;
     const float* mysrc = src + (size_t)(row_ok ? i : 0) * w;
     // batch n: row i's cursor is c = n*B - K*i.  First batch: the top row needs its first AHEAD + LEADB*B columns requested.
     const int n_first = -((AHEAD + LEADB * B + B - 1) / B);
@@ -209,19 +212,24 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
                 // lane fills its own hole, all of them in parallel, with the same bisection on its private window
                 if (hole) {
                     int vals[NWIN];
-                    int cnt = 0;
+                    int cnt = 0, vlo = 0x7fffffff, vhi = 0;
 #pragma unroll
                     for (int a = -RH; a <= RH; ++a)
 #pragma unroll
                         for (int e = -RW; e <= RW; ++e) {
-                            const float v = ring[(size_t)(i + a) * RING + ((x + e) & (RING - 1))];
+                            const float v = ring[(size_t)(i + a) * RS + ((x + e) & (RING - 1))];
                             const bool ok = v <= vmax;
-                            vals[(a + RH) * WW + (e + RW)] = ok ? (int)v : 0x7fffffff;  // float -> int truncation (:619)
+                            const int iv = ok ? (int)v : 0x7fffffff;  // float -> int truncation (:619)
+                            vals[(a + RH) * WW + (e + RW)] = iv;
                             cnt += ok ? 1 : 0;
+                            vlo = min(vlo, iv);
+                            vhi = ok ? max(vhi, iv) : vhi;
                         }
                     if (cnt > NWIN / 2) {
+                        // the median lies between the smallest and the largest valid value: neighbouring disparities are
+                        // close, so the bisection usually needs one or two rounds instead of log2(D)
                         const int need = cnt / 2 + 1;
-                        int lo = 0, hi = d - 1;
+                        int lo = vlo, hi = vhi;
                         while (lo < hi) {
                             const int mid = (lo + hi) >> 1;
                             int le = 0;
@@ -249,7 +257,7 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
                 int val = 0x7fffffff;
                 if (lane < NWIN) {
                     const int a = lane / WW - RH, e = lane % WW - RW;
-                    const float v = ring[(size_t)(i0 + a) * RING + ((x0 + e) & (RING - 1))];
+                    const float v = ring[(size_t)(i0 + a) * RS + ((x0 + e) & (RING - 1))];
                     ok = v <= vmax;
                     if (ok) val = (int)v;  // float -> int truncation (src/Solver.cpp:619)
                 }
@@ -269,7 +277,7 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
                     if (lane == 0) {
                         const float fill = (float)lo;
                         f[(size_t)i0 * w + x0] = fill;
-                        ring[(size_t)i0 * RING + (x0 & (RING - 1))] = fill;  // later columns of this row, and everyone after the barrier
+                        ring[(size_t)i0 * RS + (x0 & (RING - 1))] = fill;  // later columns of this row, and everyone after the barrier
                     }
                 }
                 __syncwarp();
@@ -384,11 +392,20 @@ void launch_median_fill(const float* src, float* f, int h, int w, int d, int win
     if (threads > 1024) threads = 1024;
     const size_t ring_bytes = (size_t)h * 32 * sizeof(float);
     static const bool legacy = std::getenv("SGM_B200_MEDIAN_LEGACY") != nullptr;
-    if (!legacy && win_h == 5 && win_w == 5 && h <= 1024 && (size_t)h * 64 * sizeof(float) <= 200 * 1024) {
+    if (!legacy && win_h == 5 && win_w == 5 && h <= 1024 && (size_t)h * 65 * sizeof(float) <= 200 * 1024) {
         // batched wavefront: skew 6, 4 columns per barrier, 64-column rings
-        const size_t bytes = (size_t)h * 64 * sizeof(float);
-        cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-        median_fill_batch_kernel<5, 5, 6, 64, 3><<<1, threads, bytes, st>>>(src, f, h, w, d);
+        const size_t bytes = (size_t)h * 65 * sizeof(float);  // rows padded to RING + 1 floats
+        static const int coop = [] { const char* e = std::getenv("SGM_B200_MEDIAN_COOP"); return e ? std::atoi(e) : 2; }();
+        if (coop == 1) {
+            cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+            median_fill_batch_kernel<5, 5, 6, 64, 3, 1><<<1, threads, bytes, st>>>(src, f, h, w, d);
+        } else if (coop == 0) {
+            cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+            median_fill_batch_kernel<5, 5, 6, 64, 3, 0><<<1, threads, bytes, st>>>(src, f, h, w, d);
+        } else {
+            cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+            median_fill_batch_kernel<5, 5, 6, 64, 3, 2><<<1, threads, bytes, st>>>(src, f, h, w, d);
+        }
     } else if (win_h == 5 && win_w == 5 && ring_bytes <= 200 * 1024 && h <= 2048 && d <= 65536) {
         // shared-memory ring form (the common case); the L2 form below stays as the fallback for very tall images
         if (h <= 1024) {
