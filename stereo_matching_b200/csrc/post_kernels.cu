@@ -263,17 +263,21 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
                 }
                 const int cnt = __popc(__ballot_sync(FULL_MASK, ok));
                 if (cnt > NWIN / 2) {
-                    // sorted[cnt / 2] by ranking: every window lane counts the values that sort before its own (ties broken
-                    // by lane, invalid entries are INT_MAX and sort last); the NWIN shuffles are independent, so this is
-                    // one shuffle latency plus the adds instead of log2(D) dependent ballot rounds
-                    int rank = 0;
-#pragma unroll
-                    for (int q = 0; q < NWIN; ++q) {
-                        const int o = __shfl_sync(FULL_MASK, val, q);
-                        rank += (o < val || (o == val && q < lane)) ? 1 : 0;
+                    // sorted[cnt / 2] = the smallest value v with at least cnt / 2 + 1 window values <= v: a bisection on
+                    // ballots between the smallest and the largest valid value (two warp reductions).  Neighbouring
+                    // disparities are close, so it takes zero to three rounds; ranking every value against every other
+                    // (25 shuffles) took longer.
+                    int lo = __reduce_min_sync(FULL_MASK, val);
+                    int hi = __reduce_max_sync(FULL_MASK, ok ? val : -1);
+                    const int need = cnt / 2 + 1;
+                    while (lo < hi) {
+                        const int mid = (lo + hi) >> 1;
+                        const int le = __popc(__ballot_sync(FULL_MASK, val <= mid));  // invalid entries are INT_MAX
+                        if (le >= need)
+                            hi = mid;
+                        else
+                            lo = mid + 1;
                     }
-                    const unsigned pick = __ballot_sync(FULL_MASK, lane < NWIN && rank == cnt / 2);
-                    const int lo = __shfl_sync(FULL_MASK, val, __ffs(pick) - 1);
                     if (lane == 0) {
                         const float fill = (float)lo;
                         f[(size_t)i0 * w + x0] = fill;
@@ -399,6 +403,12 @@ void launch_median_fill(const float* src, float* f, int h, int w, int d, int win
         if (coop == 1) {
             cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
             median_fill_batch_kernel<5, 5, 6, 64, 3, 1><<<1, threads, bytes, st>>>(src, f, h, w, d);
+        } else if (coop == 4) {
+            cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+            median_fill_batch_kernel<5, 5, 6, 64, 3, 4><<<1, threads, bytes, st>>>(src, f, h, w, d);
+        } else if (coop == 8) {
+            cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+            median_fill_batch_kernel<5, 5, 6, 64, 3, 8><<<1, threads, bytes, st>>>(src, f, h, w, d);
         } else if (coop == 0) {
             cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
             median_fill_batch_kernel<5, 5, 6, 64, 3, 0><<<1, threads, bytes, st>>>(src, f, h, w, d);
