@@ -202,11 +202,24 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
         // c + b, then for each such hole 25 lanes gather one window element each and the median comes from a bisection
         // on ballots (the values are integers in [0, D-1]).  Columns b = 0 .. B-1 go in order because a fill changes what
         // the next column of the same row sees; different rows of a batch are independent (see above).
-#pragma unroll 1
+        // Which pixels of the batch are holes is known up front (a fill only ever writes the hole it fills, and every
+        // position is examined once), so the B shared-memory reads and votes are issued together instead of one
+        // dependent read -> compare -> vote chain per column; columns without a hole in this warp then cost nothing.
+        unsigned votes[B];
+#pragma unroll
         for (int b = 0; b < B; ++b) {
             const int x = c + b;
-            const bool hole = interior_row && x >= RW && x < w - RW && !(myring[x & (RING - 1)] <= vmax);
-            unsigned todo = __ballot_sync(FULL_MASK, hole);
+            const bool hole_b = interior_row && x >= RW && x < w - RW && !(myring[x & (RING - 1)] <= vmax);
+            votes[b] = __ballot_sync(FULL_MASK, hole_b);
+        }
+#pragma unroll 1
+        for (int b = 0; b < B; ++b) {
+            unsigned todo = votes[0];
+#pragma unroll
+            for (int q = 1; q < B; ++q) todo = b == q ? votes[q] : todo;
+            if (todo == 0) continue;
+            const int x = c + b;
+            const bool hole = (todo >> lane) & 1u;
             if (__popc(todo) > COOP_MAX) {
                 // many rows of this warp have a hole in this column (occlusion bands, the invalid left margin): every such
                 // lane fills its own hole, all of them in parallel, with the same bisection on its private window
