@@ -179,6 +179,7 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
     const bool interior_row = i >= RH && i < h - RH;
     float* myring = ring + (size_t)(row_ok ? i : 0) * RS;
     const float* mysrc = src + (size_t)(row_ok ? i : 0) * w;
+    const unsigned myring_s = (unsigned)__cvta_generic_to_shared(myring);  // shared-space address: offsets fold into the cp.async
     // batch n: row i's cursor is c = n*B - K*i.  First batch: the top row needs its first AHEAD + LEADB*B columns requested.
     const int n_first = -((AHEAD + LEADB * B + B - 1) / B);
     const int n_last = ((w - 1) + K * (h - 1)) / B;
@@ -190,7 +191,7 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
             for (int b = 0; b < B; ++b) {
                 const int x = cf + b;
                 if (x >= 0 && x < w) {
-                    const unsigned dst = (unsigned)__cvta_generic_to_shared(myring + (x & (RING - 1)));
+                    const unsigned dst = myring_s + (unsigned)(x & (RING - 1)) * 4u;
                     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(mysrc + x));
                 }
             }
