@@ -411,24 +411,22 @@ void launch_median_fill(const float* src, float* f, int h, int w, int d, int win
     const size_t ring_bytes = (size_t)h * 32 * sizeof(float);
     static const bool legacy = std::getenv("SGM_B200_MEDIAN_LEGACY") != nullptr;
     if (!legacy && win_h == 5 && win_w == 5 && h <= 1024 && (size_t)h * 65 * sizeof(float) <= 200 * 1024) {
-        // batched wavefront: skew 6, 4 columns per barrier, 64-column rings
+        // batched wavefront with 64-column rings
         const size_t bytes = (size_t)h * 65 * sizeof(float);  // rows padded to RING + 1 floats
-        static const int coop = [] { const char* e = std::getenv("SGM_B200_MEDIAN_COOP"); return e ? std::atoi(e) : 2; }();
-        if (coop == 1) {
-            cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-            median_fill_batch_kernel<5, 5, 6, 64, 3, 1><<<1, threads, bytes, st>>>(src, f, h, w, d);
-        } else if (coop == 4) {
-            cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-            median_fill_batch_kernel<5, 5, 6, 64, 3, 4><<<1, threads, bytes, st>>>(src, f, h, w, d);
-        } else if (coop == 8) {
-            cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-            median_fill_batch_kernel<5, 5, 6, 64, 3, 8><<<1, threads, bytes, st>>>(src, f, h, w, d);
-        } else if (coop == 0) {
-            cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-            median_fill_batch_kernel<5, 5, 6, 64, 3, 0><<<1, threads, bytes, st>>>(src, f, h, w, d);
-        } else {
-            cudaFuncSetAttribute(median_fill_batch_kernel<5, 5, 6, 64, 3, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-            median_fill_batch_kernel<5, 5, 6, 64, 3, 2><<<1, threads, bytes, st>>>(src, f, h, w, d);
+        // Shape: skew 4 (2 columns per barrier), feeds 3 batches ahead, up to 2 cooperative fills per warp and column.  The
+        // time goes with the number of column steps W + K*H, not with the number of barriers (measured, K = 3 ... 10:
+        // profiles/r01_v13_summary.md), so the smallest skew that still amortises the barrier wins.
+        // SGM_B200_MEDIAN_SHAPE=6 selects the earlier skew-6 shape, =40 / =41 the per-lane-only / one-cooperative-fill forms.
+        static const int shape = [] { const char* e = std::getenv("SGM_B200_MEDIAN_SHAPE"); return e ? std::atoi(e) : 4; }();
+        auto run = [&](auto kern) {
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+            kern<<<1, threads, bytes, st>>>(src, f, h, w, d);
+        };
+        switch (shape) {
+            case 6: run(median_fill_batch_kernel<5, 5, 6, 64, 3, 2>); break;
+            case 40: run(median_fill_batch_kernel<5, 5, 4, 64, 3, 0>); break;
+            case 41: run(median_fill_batch_kernel<5, 5, 4, 64, 3, 1>); break;
+            default: run(median_fill_batch_kernel<5, 5, 4, 64, 3, 2>); break;
         }
     } else if (win_h == 5 && win_w == 5 && ring_bytes <= 200 * 1024 && h <= 2048 && d <= 65536) {
         // shared-memory ring form (the common case); the L2 form below stays as the fallback for very tall images
