@@ -56,6 +56,24 @@ def test_validation_errors_before_touching_the_device(lib):
     assert lib.sgm_create(None, None) == 1
 
 
+def test_integer_mode_parameter_checks_before_touching_the_device(lib):
+    # SGM_FLAG_INTEGER is only accepted where every number on the path is an integer below 2^15:
+    # a cost filter, penalties that overflow 16 bits, P1 > P2, D = 32 or a BM algorithm are refused with SGM_ERR_UNSUPPORTED
+    bad = (dict(), dict(box_w=1, box_h=1, P2=5000), dict(box_w=1, box_h=1, P1=20, P2=10), dict(box_w=1, box_h=3),
+           dict(box_w=1, box_h=1, flags=capi.FLAG_INTEGER | capi.FLAG_LINE_WALKERS))
+    for over in bad:
+        p = capi.default_params(64, 64, 1, 64, flags=capi.FLAG_INTEGER)
+        for k, v in over.items():
+            setattr(p, k, v)
+        handle = C.c_void_p()
+        assert lib.sgm_create(C.byref(handle), C.byref(p)) == 2, over
+        assert handle.value is None and b"SGM_FLAG_INTEGER" in lib.sgm_last_error(None)
+    p = capi.default_params(64, 64, 1, 32, flags=capi.FLAG_INTEGER, box_w=1, box_h=1)
+    assert lib.sgm_create(C.byref(C.c_void_p()), C.byref(p)) == 2
+    p = capi.default_params(64, 64, 1, 64, algo=capi.ALGO_BM, flags=capi.FLAG_INTEGER, box_w=1, box_h=1)
+    assert lib.sgm_create(C.byref(C.c_void_p()), C.byref(p)) == 2
+
+
 def test_no_cpu_fallback_without_a_device(lib):
     import torch
 
