@@ -19,6 +19,11 @@
 // neighbours' PREVIOUS row, so all blocks advance within one row of their neighbours; the kernel is launched
 // cooperatively so that every block is resident, and every wait has a time-out that raises an error flag instead of
 // hanging.
+//
+// The kernels are written once for both arithmetics: they move a pixel's vector as 32-bit words (`float` registers) and
+// leave every operation on the values to a policy class AR (sgm_device.cuh): F32Arith<D> is the reference's float32
+// arithmetic (one word = one cost), S16x2Arith<D/2> the integer / DPX mode (one word = two 16-bit costs, SGM_FLAG_INTEGER).
+// The template parameter D of a kernel is the number of WORDS per pixel.
 #include <cstdlib>
 #include <cstring>
 
