@@ -314,10 +314,25 @@ __device__ __forceinline__ int uf_root(const int* label, int x) {
         x = p;
     }
 }
+// Root with path halving, for the merge pass: every second node on the way is re-pointed at its grandparent, so the
+// chains through the rows of a tall component (one hop per row, each an L2 round trip) shrink as the merge proceeds.
+// Safe beside the atomicMin of uf_unite: a parent always has a smaller index than its child (no cycles), only non-roots
+// are re-pointed (a node that has a parent never becomes a root again, so a successful hang of a root is never
+// overwritten), and the new target is an ancestor, i.e. still inside the component.
+__device__ __forceinline__ int uf_root_halving(int* label, int x) {
+    while (true) {
+        const int p = __ldcg(label + x);
+        if (p == x) return x;
+        const int g = __ldcg(label + p);
+        if (g == p) return p;
+        __stcg(label + x, g);
+        x = g;
+    }
+}
 __device__ __forceinline__ void uf_unite(int* label, int a, int b) {
     while (true) {
-        a = uf_root(label, a);
-        b = uf_root(label, b);
+        a = uf_root_halving(label, a);
+        b = uf_root_halving(label, b);
         if (a == b) return;
         if (a < b) {
             const int t = a;
