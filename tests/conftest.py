@@ -19,3 +19,13 @@ def golden():
     with open(os.path.join(ROOT, "tests", "golden", "kat_hashes.json")) as f:
         data = json.load(f)
     return {c["name"]: c for c in data["cases"]}
+
+
+@pytest.fixture(scope="session")
+def golden_integer():
+    """KITTI-size vectors of the integer / DPX mode (tests/golden/make_golden_integer.py: restatement, window 1x1)."""
+    import json
+
+    with open(os.path.join(ROOT, "tests", "golden", "kat_hashes_integer.json")) as f:
+        data = json.load(f)
+    return {c["name"]: c for c in data["cases"]}

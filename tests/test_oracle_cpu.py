@@ -128,6 +128,18 @@ def test_integer_restatement_equals_float_restatement_without_cost_filter(h, w, 
         assert np.array_equal(Si.astype(np.float32), S)
 
 
+def test_integer_mode_golden_is_reproducible(golden_integer):
+    # tests/golden/kat_hashes_integer.json must be what the restatement (window 1x1) produces today
+    c = golden_integer["kitti_int_d64_scale2"]
+    L, R, _ = synth.random_dot_pair(c["h"], c["w"], seed=c["seed"], bg=c["bg"], fg=c["fg"], noise=c["noise"])
+    s = c["scale"]
+    out = restate.process(L, R, s, c["d"], "sgm", taps=("S", "disp", "f_final"), box_w=s, box_h=s)
+    want = c["hashes"]
+    assert (H(L), H(R)) == (want["left"], want["right"])
+    assert H(out["S"][0]) == want["S_l"] and H(out["disp"][1]) == want["disp_beta"] and H(out["f_final"]) == want["f_final"]
+    assert int(out["S"][0].max()) == c["stats"]["S_max"] <= 8 * (62 + 100)
+
+
 def test_widened_restatement_runs_d256():
     # D=256 cannot run through the reference (src/Solver.cpp:10 asserts); the restatement is the oracle there
     L, R, _ = synth.random_dot_pair(48, 400, seed=4, bg=24, fg=200, noise=4)

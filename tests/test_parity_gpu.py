@@ -131,6 +131,25 @@ def test_integer_mode_equals_float_mode_at_kitti_size():
     a.close(), b.close()
 
 
+@pytest.mark.parametrize("name", ["kitti_int_d128_noisy", "kitti_int_d64_clean", "kitti_int_d64_scale2"])
+def test_integer_mode_kitti_size_against_golden(golden_integer, name):
+    # full BASELINE.json size against the committed vectors of the oracle (restatement with the cost filter at 1x1,
+    # cross-checked with its 16-bit form when they were generated): every tap by hash, no oracle run on the GPU box
+    c = golden_integer[name]
+    L, R, _ = synth.random_dot_pair(c["h"], c["w"], seed=c["seed"], bg=c["bg"], fg=c["fg"], noise=c["noise"])
+    want, s = c["hashes"], c["scale"]
+    assert (H(L), H(R)) == (want["left"], want["right"])
+    sv = capi.SGM(c["h"], c["w"], s, c["d"], flags=capi.FLAG_INTEGER | capi.FLAG_KEEP_VOLUMES, box_w=s, box_h=s)
+    sv.process(L, R)
+    got = dict(cost_l=H(sv.tap("cost", 0)), cost_r=H(sv.tap("cost", 1)), S_l=H(sv.tap("pathsum", 0)), S_r=H(sv.tap("pathsum", 1)),
+               disp=H(sv.tap("disp", 0)), disp_beta=H(sv.tap("disp", 1)), fsub_l=H(sv.tap("subpixel", 0)),
+               fsub_r=H(sv.tap("subpixel", 1)), f_lr=H(sv.tap("lr")), f_median=H(sv.tap("median")), f_final=H(sv.get_disp()))
+    bad = sorted(k for k, v in got.items() if v != want[k])
+    assert not bad, f"{name}: taps whose hash differs from the oracle's golden vectors: {bad}"
+    assert int((sv.get_disp() <= c["d"] - 1).sum()) == c["stats"]["valid"]
+    sv.close()
+
+
 def test_integer_mode_rejects_what_it_cannot_represent():
     for over in (dict(), dict(box_w=1, box_h=1, P2=5000), dict(box_w=1, box_h=1, P1=20, P2=10)):
         with pytest.raises(capi.SgmError) as e:
