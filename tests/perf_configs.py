@@ -43,7 +43,7 @@ CONFIGS = [
 
 def run(name, cls, h, w, d, gen, frames):
     pairs = [synth.random_dot_pair(h, w, seed=100 + k, noise=4 if k else 0, **gen)[:2] for k in range(4)]
-    inflight = 5 if h * w * d < 3e8 else 2
+    inflight = 5 if h * w * d < 3e8 else 3
     engines = [cls(h, w, 1, d) for _ in range(inflight)]
     probe = cls(h, w, 1, d, flags=capi.FLAG_STAGE_TIMING)
     fs = stream.FrameStream(engines)
