@@ -183,16 +183,21 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
     // batch n: row i's cursor is c = n*B - K*i.  First batch: the top row needs its first AHEAD + LEADB*B columns requested.
     const int n_first = -((AHEAD + LEADB * B + B - 1) / B);
     const int n_last = ((w - 1) + K * (h - 1)) / B;
-    for (int n = n_first; n <= n_last; ++n) {
-        const int c = n * B - K * i;
-        if (row_ok) {
+    // The batch loop is a chain of dependent instructions executed ~W + K*H times, so everything that does not change is
+    // kept out of it: the cursor and the feed address advance by B, range tests are single unsigned compares.
+    int c = n_first * B - K * i;
+    long long feed = (long long)(size_t)mysrc + 4ll * (c + AHEAD + LEADB * B);  // address of column c + AHEAD + LEADB*B of this row
+    const unsigned feed_lim = row_ok ? (unsigned)w : 0u;                       // columns [0, w) are fed
+    const unsigned hole_lim = interior_row ? (unsigned)(w - 2 * RW) : 0u;       // columns [RW, w - RW) can be holes
+    for (int n = n_first; n <= n_last; ++n, c += B, feed += 4 * B) {
+        {
             const int cf = c + AHEAD + LEADB * B;
 #pragma unroll
             for (int b = 0; b < B; ++b) {
                 const int x = cf + b;
-                if (x >= 0 && x < w) {
+                if ((unsigned)x < feed_lim) {
                     const unsigned dst = myring_s + (unsigned)(x & (RING - 1)) * 4u;
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(mysrc + x));
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(feed + 4 * b));
                 }
             }
         }
@@ -210,8 +215,8 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
 #pragma unroll
         for (int b = 0; b < B; ++b) {
             const int x = c + b;
-            const bool hole_b = interior_row && x >= RW && x < w - RW && !(myring[x & (RING - 1)] <= vmax);
-            votes[b] = __ballot_sync(FULL_MASK, hole_b);
+            const float v = myring[x & (RING - 1)];  // any slot is readable; the range test decides whether it counts
+            votes[b] = __ballot_sync(FULL_MASK, (unsigned)(x - RW) < hole_lim && !(v <= vmax));
         }
 #pragma unroll 1
         for (int b = 0; b < B; ++b) {

@@ -1,5 +1,5 @@
-# dev helper: parity twice + both bench modes (one gpurun call)
-for k in 1 2; do python -m pytest tests -m gpu -x -q 2>&1 | tail -1; done
+# dev helper: parity + both bench modes (one gpurun call)
+python -m pytest tests -m gpu -x -q 2>&1 | tail -1
 for m in reference integer; do
 python bench.py --mode $m --no-cpu-baseline --steps 10 2>/dev/null | python -c "
 import json,sys
