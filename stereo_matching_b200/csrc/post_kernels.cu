@@ -171,15 +171,22 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
     constexpr int RS = RING + 1;
     extern __shared__ float ring[];  // [h][RS]
     const float vmax = (float)(d - 1);
-    const int i = threadIdx.x;       // one row per thread (h <= blockDim.x)
-    const int lane = threadIdx.x & 31;
+    // Values that never change are pinned in registers through opaque moves: left alone, the compiler re-derives them in
+    // every batch (S2R tid, the shared window base, the row's limits), which lengthens the loop's dependent chain.
+    auto pin = [](unsigned v) {
+        unsigned r;
+        asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(v));
+        return r;
+    };
+    const int i = (int)pin(threadIdx.x);  // one row per thread (h <= blockDim.x)
+    const int lane = i & 31;
     static_assert(NWIN <= 32, "the window must fit a warp");
     // COOP_MAX: up to this many holes per warp and column are filled one after the other by the whole warp
     const bool row_ok = i < h;
     const bool interior_row = i >= RH && i < h - RH;
     float* myring = ring + (size_t)(row_ok ? i : 0) * RS;
     const float* mysrc = src + (size_t)(row_ok ? i : 0) * w;
-    const unsigned myring_s = (unsigned)__cvta_generic_to_shared(myring);  // shared-space address: offsets fold into the cp.async
+    const unsigned myring_s = pin((unsigned)__cvta_generic_to_shared(myring));  // shared-space address: offsets fold into the cp.async
     // batch n: row i's cursor is c = n*B - K*i.  First batch: the top row needs its first AHEAD + LEADB*B columns requested.
     const int n_first = -((AHEAD + LEADB * B + B - 1) / B);
     const int n_last = ((w - 1) + K * (h - 1)) / B;
@@ -187,8 +194,8 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
     // kept out of it: the cursor and the feed address advance by B, range tests are single unsigned compares.
     int c = n_first * B - K * i;
     long long feed = (long long)(size_t)mysrc + 4ll * (c + AHEAD + LEADB * B);  // address of column c + AHEAD + LEADB*B of this row
-    const unsigned feed_lim = row_ok ? (unsigned)w : 0u;                       // columns [0, w) are fed
-    const unsigned hole_lim = interior_row ? (unsigned)(w - 2 * RW) : 0u;       // columns [RW, w - RW) can be holes
+    const unsigned feed_lim = pin(row_ok ? (unsigned)w : 0u);                  // columns [0, w) are fed
+    const unsigned hole_lim = pin(interior_row ? (unsigned)(w - 2 * RW) : 0u);  // columns [RW, w - RW) can be holes
     for (int n = n_first; n <= n_last; ++n, c += B, feed += 4 * B) {
         {
             const int cf = c + AHEAD + LEADB * B;
@@ -215,7 +222,8 @@ __global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __
 #pragma unroll
         for (int b = 0; b < B; ++b) {
             const int x = c + b;
-            const float v = myring[x & (RING - 1)];  // any slot is readable; the range test decides whether it counts
+            float v;  // any slot is readable; the range test decides whether it counts
+            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(myring_s + (unsigned)(x & (RING - 1)) * 4u));
             votes[b] = __ballot_sync(FULL_MASK, (unsigned)(x - RW) < hole_lim && !(v <= vmax));
         }
 #pragma unroll 1
