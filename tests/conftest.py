@@ -29,3 +29,14 @@ def golden_integer():
     with open(os.path.join(ROOT, "tests", "golden", "kat_hashes_integer.json")) as f:
         data = json.load(f)
     return {c["name"]: c for c in data["cases"]}
+
+
+@pytest.fixture(scope="session")
+def golden_fullsize():
+    """Full-size vectors of the configurations the reference cannot run: 1920x1080 D=256 (float and integer mode) and SAD
+    block matching at 1242x375 (tests/golden/make_golden_fullsize.py: widened restatement)."""
+    import json
+
+    with open(os.path.join(ROOT, "tests", "golden", "kat_hashes_fullsize.json")) as f:
+        data = json.load(f)
+    return {c["name"]: c for c in data["cases"]}

@@ -140,6 +140,20 @@ def test_integer_mode_golden_is_reproducible(golden_integer):
     assert int(out["S"][0].max()) == c["stats"]["S_max"] <= 8 * (62 + 100)
 
 
+@pytest.mark.parametrize("name", ["kitti_bmsad_d64_noisy", "hd_sgm_d256_clean"])
+def test_fullsize_golden_is_reproducible(golden_fullsize, name):
+    # tests/golden/kat_hashes_fullsize.json (the configurations the reference cannot run, at BASELINE.json's full sizes)
+    # must be what the widened restatement produces today; the 1080p case takes about a minute
+    c = golden_fullsize[name]
+    L, R, _ = synth.random_dot_pair(c["h"], c["w"], seed=c["seed"], bg=c["bg"], fg=c["fg"], noise=c["noise"])
+    out = restate.process(L, R, c["scale"], c["d"], c["algo"], taps=("disp", "fsub", "f_lr", "f_median", "f_final"))
+    want = c["hashes"]
+    assert (H(L), H(R)) == (want["left"], want["right"])
+    assert H(out["disp"][0]) == want["disp_l"] and H(out["disp"][1]) == want["disp_r"] and H(out["fsub"][1]) == want["fsub_r"]
+    assert H(out["f_lr"]) == want["f_lr"] and H(out["f_median"]) == want["f_median"] and H(out["f_final"]) == want["f_final"]
+    assert int((out["f_final"] <= c["d"] - 1).sum()) == c["stats"]["valid"]
+
+
 def test_widened_restatement_runs_d256():
     # D=256 cannot run through the reference (src/Solver.cpp:10 asserts); the restatement is the oracle there
     L, R, _ = synth.random_dot_pair(48, 400, seed=4, bg=24, fg=200, noise=4)

@@ -338,22 +338,73 @@ def test_error_codes_instead_of_asserts():
     sv.close()
 
 
-def test_full_size_1080p_d256_properties():
-    # BASELINE.json config 4: the reference cannot run it; check size-independent properties at full size
-    h, w, d = 1080, 1920, 256
-    L, R, gt = synth.random_dot_pair(h, w, seed=31, bg=24, fg=200)
-    sv = capi.SGM(h, w, 1, d)
-    f1 = sv.process(L, R).get_disp()
-    f2 = sv.process(L, R).get_disp()
-    assert bits_equal(f1, f2)                                   # deterministic
+def _hd_taps(sv):
+    got = {}
+    for v, sfx in ((0, "_l"), (1, "_r")):
+        got["census" + sfx] = H(sv.tap("census", v))
+        got["cost_hv" + sfx] = H(sv.tap("cost", v))
+        got["S" + sfx] = H(sv.tap("pathsum", v))
+        got["disp" + sfx] = H(sv.tap("disp", v))
+        got["fsub" + sfx] = H(sv.tap("subpixel", v))
+    got.update(f_lr=H(sv.tap("lr")), f_median=H(sv.tap("median")), f_final=H(sv.get_disp()))
+    return got
+
+
+@pytest.mark.parametrize("name", ["hd_sgm_d256_clean", "hd_sgm_d256_noisy", "hd_int_d256_noisy"])
+def test_full_size_1080p_d256_against_golden(golden_fullsize, name):
+    # BASELINE.json configs[3] (1920x1080, D=256, 8 paths) at its full size, every tap by hash against the widened
+    # restatement (tests/golden/make_golden_fullsize.py; the reference asserts d <= 128, src/Solver.cpp:10).  This size takes
+    # code paths no smaller test reaches: one view per sweep launch (the two views do not fit a resident cooperative grid),
+    # 8 words per lane, the tall-image median.
+    c = golden_fullsize[name]
+    h, w, d = c["h"], c["w"], c["d"]
+    L, R, gt = synth.random_dot_pair(h, w, seed=c["seed"], bg=c["bg"], fg=c["fg"], noise=c["noise"])
+    want = c["hashes"]
+    assert (H(L), H(R)) == (want["left"], want["right"])
+    over = dict(box_w=1, box_h=1, flags=capi.FLAG_KEEP_VOLUMES | capi.FLAG_INTEGER) if c["integer"] else dict(flags=capi.FLAG_KEEP_VOLUMES)
+    sv = capi.SGM(h, w, 1, d, **over)
+    sv.process(L, R)
+    got = _hd_taps(sv)
+    bad = sorted(k for k, v in got.items() if v != want[k])
+    assert not bad, f"{name}: taps whose hash differs from the widened restatement: {bad}"
+    f1 = sv.get_disp()
+    assert int((f1 <= d - 1).sum()) == c["stats"]["valid"]
+    assert int((sv.tap("median").view(np.uint32) != sv.tap("lr").view(np.uint32)).sum()) == c["stats"]["holes_filled"]
+    # size-independent properties on top of the hashes: the handle is reusable and deterministic, the result is close to
+    # the ground truth, invalid pixels carry exactly D+1
+    assert bits_equal(sv.process(L, R).get_disp(), f1)
     valid = f1 <= d - 1
     cols = np.arange(w)[None, :] >= d
-    good = valid & cols & (np.abs(f1 - gt) <= 1)
-    assert good.sum() > 0.9 * cols.sum() * h / h and (valid & cols).mean() > 0.7
-    d16 = sv.get_disp_u16(0)
-    assert d16.max() <= d + 1 and set(np.unique(f1[~valid])) == {float(d + 1)}
-    # a frame that is constant along x has no texture: identical left/right => disparity 0 or invalid everywhere
-    flat = np.repeat(np.arange(h, dtype=np.uint8)[:, None] * 3, w, axis=1)
-    f3 = sv.process(flat, flat).get_disp()
-    assert set(np.unique(f3)) <= {0.0, float(d + 1)}
+    assert ((valid & cols & (np.abs(f1 - gt) <= 1)).sum() > 0.9 * cols.sum() * h) and set(np.unique(f1[~valid])) == {float(d + 1)}
+    assert sv.get_disp_u16(0).max() <= d + 1
     sv.close()
+
+
+def test_full_size_1080p_flat_frame_has_no_texture():
+    # a frame that is constant along x has no texture: identical left / right => disparity 0 or invalid everywhere
+    h, w, d = 1080, 1920, 256
+    flat = np.repeat(np.arange(h, dtype=np.uint8)[:, None] * 3, w, axis=1)
+    sv = capi.SGM(h, w, 1, d)
+    assert set(np.unique(sv.process(flat, flat).get_disp())) <= {0.0, float(d + 1)}
+    sv.close()
+
+
+@pytest.mark.parametrize("name", ["kitti_bmsad_d64_clean", "kitti_bmsad_d64_noisy"])
+def test_bm_sad_kitti_size_against_golden(golden_fullsize, name):
+    # BASELINE.json configs[1]: SAD 9x9 block matching + WTA + LR-check at 1242x375, D=64, every tap by hash against the
+    # restatement built on the reference's own SAD() (src/cost.cpp:4-30; pinned in tests/test_oracle_cpu.py)
+    c = golden_fullsize[name]
+    L, R, _ = synth.random_dot_pair(c["h"], c["w"], seed=c["seed"], bg=c["bg"], fg=c["fg"], noise=c["noise"])
+    want = c["hashes"]
+    assert (H(L), H(R)) == (want["left"], want["right"])
+    bm = capi.BMSad(c["h"], c["w"], c["scale"], c["d"])
+    bm.process(L, R)
+    got = dict(f_lr=H(bm.tap("lr")), f_median=H(bm.tap("median")), f_final=H(bm.get_disp()))
+    for v, sfx in ((0, "_l"), (1, "_r")):
+        got["cost_raw" + sfx] = H(bm.tap("cost", v))
+        got["disp" + sfx] = H(bm.tap("disp", v))
+        got["fsub" + sfx] = H(bm.tap("subpixel", v))
+    bad = sorted(k for k, v in got.items() if v != want[k])
+    assert not bad, f"{name}: taps whose hash differs from the restatement: {bad}"
+    assert int((bm.get_disp() <= c["d"] - 1).sum()) == c["stats"]["valid"]
+    bm.close()
