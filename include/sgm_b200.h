@@ -77,6 +77,11 @@ typedef struct sgm_params {
  * instructions VIMNMX3 / VIADDMNMX.  Results are IDENTICAL to the float path under the same parameters (tested tap by tap);
  * sgm_create rejects parameter sets for which that would not hold (SGM_ERR_UNSUPPORTED). */
 #define SGM_FLAG_INTEGER 0x8u
+/* The C++ shells keep Solver's protected result Mats (disp, disp_beta, filtered_disp_beta: inc/Solver.h:43-46) filled after every
+ * process(): with this flag the 8-bit disparities of both views (narrowed on the device) and the right view's sub-pixel image are
+ * copied to pinned host memory on the frame's stream together with the result, so sgm_get_disparity_u8 / sgm_get_subpixel_beta
+ * are plain host copies (no synchronous cudaMemcpy, no allocation). */
+#define SGM_FLAG_HOST_TAPS 0x10u
 #define SGM_FLAG_STAGE_TIMING 0x2u /* record CUDA events around the pipeline stages on the engine's stream (sgm_get_stage_ms) */
 
 /* Buffers readable after a frame, for parity tests and debugging (the reference keeps the same data in
@@ -136,6 +141,8 @@ SGM_API int sgm_get_disparity_f32(sgm_engine* e, float* dst, size_t dst_stride);
 /* Solver::disp / disp_beta narrowed to 8 bits like the reference's CV_8UC1 Mats (only for D <= 128). */
 SGM_API int sgm_get_disparity_u8(sgm_engine* e, int view, uint8_t* dst, size_t dst_stride);
 SGM_API int sgm_get_disparity_u16(sgm_engine* e, int view, uint16_t* dst, size_t dst_stride);
+/* Solver::filtered_disp_beta as SGM::process leaves it (src/SGM.cpp:801): the right view's sub-pixel disparity. */
+SGM_API int sgm_get_subpixel_beta(sgm_engine* e, float* dst, size_t dst_stride);
 /* Device pointer of the final float disparity (valid until the next frame), for device-side consumers. */
 SGM_API const float* sgm_disparity_device(sgm_engine* e);
 

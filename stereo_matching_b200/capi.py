@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libsgm_b200.so")
 
 ALGO_SGM, ALGO_BM, ALGO_BM_SAD = 0, 1, 2
-FLAG_KEEP_VOLUMES, FLAG_STAGE_TIMING, FLAG_LINE_WALKERS, FLAG_INTEGER = 1, 2, 4, 8
+FLAG_KEEP_VOLUMES, FLAG_STAGE_TIMING, FLAG_LINE_WALKERS, FLAG_INTEGER, FLAG_HOST_TAPS = 1, 2, 4, 8, 16
 TAP = dict(census=0, cost=1, pathsum=2, disp=3, subpixel=4, lr=5, median=6, final=7, blur=8)
 _TAP_DTYPE = dict(census=np.uint64, cost=np.float32, pathsum=np.float32, disp=np.uint16, subpixel=np.float32,
                   lr=np.float32, median=np.float32, final=np.float32, blur=np.uint8)
@@ -25,6 +25,7 @@ EXPORTS = [
     "sgm_wait", "sgm_enqueue_device", "sgm_get_disparity_f32", "sgm_get_disparity_u8", "sgm_get_disparity_u16",
     "sgm_disparity_device", "sgm_tap_bytes", "sgm_get_tap", "sgm_get_size", "sgm_get_launch_count", "sgm_get_stage_ms",
     "sgm_get_stream", "sgm_device_bytes", "sgm_cost_volume_sad", "sgm_render_debug_view", "sgm_point_cloud",
+    "sgm_get_subpixel_beta",
 ]
 
 
@@ -72,6 +73,7 @@ def lib():
         L.sgm_get_disparity_f32.argtypes = [vp, vp, sz]
         L.sgm_get_disparity_u8.argtypes = [vp, i, vp, sz]
         L.sgm_get_disparity_u16.argtypes = [vp, i, vp, sz]
+        L.sgm_get_subpixel_beta.argtypes = [vp, vp, sz]
         L.sgm_disparity_device.argtypes = [vp]
         L.sgm_disparity_device.restype = vp
         L.sgm_tap_bytes.argtypes = [vp, i]
@@ -190,6 +192,12 @@ class Solver:
     def get_disp_u16(self, view=0) -> np.ndarray:
         out = np.empty((self.img_h, self.img_w), np.uint16)
         self._check(lib().sgm_get_disparity_u16(self._h, view, out.ctypes.data, out.strides[0]))
+        return out
+
+    def get_subpixel_beta(self) -> np.ndarray:
+        """Solver::filtered_disp_beta (src/SGM.cpp:801): the right view's sub-pixel disparity."""
+        out = np.empty((self.img_h, self.img_w), np.float32)
+        self._check(lib().sgm_get_subpixel_beta(self._h, out.ctypes.data, out.strides[0]))
         return out
 
     def tap(self, name, view=0) -> np.ndarray:

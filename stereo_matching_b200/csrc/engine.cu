@@ -12,61 +12,10 @@
 #include <string>
 #include <vector>
 
-#include "../../include/sgm_b200.h"
+#include "engine_internal.h"
 #include "kernels.h"
 
 using namespace sgmb200;
-
-struct sgm_engine {
-    sgm_params p;
-    int ih = 0, iw = 0, D = 0, views = 1;
-    size_t n = 0, N = 0;  // pixels, pixels * D (working resolution)
-    cudaStream_t stream = nullptr;
-    cudaEvent_t ev[SGM_STAGE_COUNT + 1] = {};
-    bool timing = false, have_result = false, result_on_host = false, busy = false;
-    bool integer = false;  // SGM_FLAG_INTEGER: volumes hold s16x2 words (two disparities per 32-bit word)
-    size_t vol_words = 0;  // 32-bit words per view of a volume: N (float mode) or N / 2 (integer mode)
-    int launches = 0;
-    float stage_ms[SGM_STAGE_COUNT] = {};
-    size_t device_bytes = 0;
-    std::string err;
-
-    // device
-    uint8_t* d_in[2] = {nullptr, nullptr};   // full-resolution staging of the host inputs (dense)
-    uint8_t* d_sky[2] = {nullptr, nullptr};  // [n] each
-    uint8_t* d_img = nullptr;                // [2][n] working-resolution images
-    uint8_t* d_blur = nullptr;               // [2][n]
-    uint64_t* d_census = nullptr;            // [2][n]
-    float* d_cost = nullptr;                 // [views][N]
-    float* d_acc_a = nullptr;                // [views][N]
-    float* d_acc_b = nullptr;                // [views][N]
-    float* d_pathsum = nullptr;              // [views][N] (SGM_FLAG_KEEP_VOLUMES)
-    uint16_t* d_disp = nullptr;              // [2][n]
-    float* d_sub = nullptr;                  // [2][n]
-    float* d_lr = nullptr;                   // [n]
-    float* d_med = nullptr;                  // [n]
-    float* d_final = nullptr;                // [n]
-    int* d_label = nullptr;                  // [n]
-    int* d_area = nullptr;                   // [n]
-    float* d_sad_lut = nullptr;              // SAD block matching: (sum / win_h) / win_w for every integer sum
-    float* d_halo = nullptr;                 // fused aggregation: cross-block halo ring (tagged payload)
-    unsigned halo_seq = 0;                   // fused aggregation: sweep launches so far (tag source)
-    int* d_error = nullptr;                  // fused aggregation: time-out flag
-    int* h_error = nullptr;                  // pinned copy of d_error
-    bool fused = false;                      // last frame used the fused schedule
-    // consumers of the result (allocated on first use)
-    uint8_t* d_view = nullptr;               // [2*ih][iw][3] debug view
-    int* d_pc_counts = nullptr;              // point cloud: per-block counts / offsets
-    int* d_pc_offsets = nullptr;
-    double* d_pc_xyz = nullptr;              // [n][3]
-    uint8_t* d_pc_int = nullptr;             // [n]
-    const uint8_t* last_left = nullptr;      // device pointer / stride of the last frame's full-resolution left image
-    size_t last_left_stride = 0;
-    // pinned host
-    uint8_t* h_in[2] = {nullptr, nullptr};
-    uint8_t* h_sky[2] = {nullptr, nullptr};
-    float* h_final = nullptr;
-};
 
 namespace {
 
@@ -143,6 +92,10 @@ void release(sgm_engine* e) {
     cudaFree(e->d_pc_int);
     cudaFreeHost(e->h_error);
     cudaFreeHost(e->h_final);
+    cudaFreeHost(e->h_disp8);
+    cudaFreeHost(e->h_sub_r);
+    cudaFree(e->d_disp8);
+    if (e->ev_done) cudaEventDestroy(e->ev_done);
     for (auto& ev : e->ev)
         if (ev) cudaEventDestroy(ev);
     if (e->stream) cudaStreamDestroy(e->stream);
@@ -244,6 +197,7 @@ int sgm_create(sgm_engine** out, const sgm_params* params) {
     bool ok = cudaSetDevice(p.device) == cudaSuccess;
     ok = ok && cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess;
     for (int k = 0; ok && k <= SGM_STAGE_COUNT; ++k) ok = cudaEventCreate(&e->ev[k]) == cudaSuccess;
+    ok = ok && cudaEventCreateWithFlags(&e->ev_done, cudaEventBlockingSync | cudaEventDisableTiming) == cudaSuccess;
     for (int v = 0; ok && v < 2; ++v) {
         ok = ok && dev_alloc(e, &e->d_in[v], full) == cudaSuccess;
         ok = ok && dev_alloc(e, &e->d_sky[v], e->n) == cudaSuccess;
@@ -260,8 +214,10 @@ int sgm_create(sgm_engine** out, const sgm_params* params) {
         const size_t halo_bytes = fused_halo_bytes(e->views, iw, e->D);
         ok = ok && dev_alloc(e, &e->d_halo, halo_bytes / sizeof(float)) == cudaSuccess;
         ok = ok && cudaMemset(e->d_halo, 0, halo_bytes) == cudaSuccess;
-        // test hook: start the launch sequence of the halo tags near its wrap-around (normally reached after ~5e5 frames)
+#ifdef SGM_B200_TUNING
+        // test hook (tuning build only): start the launch sequence of the halo tags near its wrap-around (normally reached after ~5e5 frames)
         if (const char* s0 = std::getenv("SGM_B200_HALO_SEQ_START")) e->halo_seq = (unsigned)std::strtoul(s0, nullptr, 0);
+#endif
         ok = ok && dev_alloc(e, &e->d_error, 1) == cudaSuccess;
         ok = ok && cudaMemset(e->d_error, 0, sizeof(int)) == cudaSuccess;
         ok = ok && cudaMallocHost(reinterpret_cast<void**>(&e->h_error), sizeof(int)) == cudaSuccess;
@@ -282,6 +238,12 @@ int sgm_create(sgm_engine** out, const sgm_params* params) {
     ok = ok && dev_alloc(e, &e->d_label, e->n) == cudaSuccess;
     ok = ok && dev_alloc(e, &e->d_area, e->n) == cudaSuccess;
     ok = ok && cudaMallocHost(reinterpret_cast<void**>(&e->h_final), e->n * sizeof(float)) == cudaSuccess;
+    e->host_taps = (p.flags & SGM_FLAG_HOST_TAPS) != 0;
+    if (e->host_taps) {
+        ok = ok && dev_alloc(e, &e->d_disp8, 2 * e->n) == cudaSuccess;
+        ok = ok && cudaMallocHost(reinterpret_cast<void**>(&e->h_disp8), 2 * e->n) == cudaSuccess;
+        ok = ok && cudaMallocHost(reinterpret_cast<void**>(&e->h_sub_r), e->n * sizeof(float)) == cudaSuccess;
+    }
     if (!ok) {
         cudaError_t last = cudaGetLastError();
         fail(nullptr, last == cudaErrorMemoryAllocation ? SGM_ERR_NOMEM : SGM_ERR_CUDA, "sgm_create: allocation failed (%s)",
@@ -351,7 +313,7 @@ int run_frame(sgm_engine* e, const uint8_t* left, size_t lstride, const uint8_t*
         a.error = e->d_error;
         a.packed16 = e->integer ? 1 : 0;
         // fused three-launch schedule (sweep_kernels.cu) unless disabled or the image is too wide for a resident sweep
-        const bool want_fused = !(p.flags & SGM_FLAG_LINE_WALKERS) && std::getenv("SGM_B200_LINE_WALKERS") == nullptr;
+        const bool want_fused = !(p.flags & SGM_FLAG_LINE_WALKERS);
         e->fused = want_fused && launch_aggregate_fused(a, st, lc);
         if (!e->fused && e->integer)
             return fail(e, SGM_ERR_UNSUPPORTED, "integer mode: the image is too wide for a resident sweep and there is no other integer schedule");
@@ -398,40 +360,124 @@ void pack_rows(uint8_t* dst, const uint8_t* src, size_t stride, int rows, int co
     for (int r = 0; r < rows; ++r) std::memcpy(dst + (size_t)r * cols, src + (size_t)r * stride, cols);
 }
 
+
+bool debug_sync() {
+#ifdef SGM_B200_TUNING
+    static const bool on = std::getenv("SGM_B200_DEBUG_SYNC") != nullptr;  // synchronise after every launch to localise a fault
+    return on;
+#else
+    return false;
+#endif
+}
+
+// A frame failed after work may already have been queued: nothing of it may be read as a result, and the pinned staging
+// must not be overwritten by the next sgm_enqueue while an earlier copy is still in flight.
+int abandon_frame(sgm_engine* e, int rc) {
+    cudaStreamSynchronize(e->stream);
+    (void)cudaGetLastError();
+    e->busy = false;
+    e->have_result = false;
+    return rc;
+}
+
+// Common tail of sgm_wait / engine_wait_blocking once the stream has drained (c = what the synchronisation returned).
+int finish_frame(sgm_engine* e, cudaError_t c) {
+    e->busy = false;
+    e->have_result = false;  // set again below, only when the frame is good
+    if (c != cudaSuccess) return fail(e, SGM_ERR_CUDA, "frame failed: %s", cudaGetErrorString(c));
+    if (e->h_error && *e->h_error) {
+        const int code = *e->h_error;
+        *e->h_error = 0;
+        cudaMemset(e->d_error, 0, sizeof(int));
+        return fail(e, SGM_ERR_CUDA, "a device-side wait timed out (code %d: blocks of a cooperative kernel not co-resident?)", code);
+    }
+    e->have_result = true;
+    if (e->timing) {
+        for (int k = 0; k < SGM_STAGE_COUNT; ++k) {
+            float ms = 0.f;
+            const int nxt = k + 1 == SGM_STAGE_COUNT ? SGM_STAGE_COUNT : k + 1;
+            if (cudaEventElapsedTime(&ms, e->ev[k], e->ev[nxt]) != cudaSuccess) ms = -1.f;
+            e->stage_ms[k] = ms;
+        }
+        (void)cudaGetLastError();
+    }
+    return SGM_OK;
+}
+
 }  // namespace
+
+namespace sgmb200 {
+
+int engine_stage(sgm_engine* e, const uint8_t* left, size_t ls, const uint8_t* right, size_t rs, const uint8_t* sky_l, size_t sls,
+                 const uint8_t* sky_r, size_t srs) {
+    int rc = check_images(e, left, ls, right, rs, sky_l, sls, sky_r, srs);
+    if (rc != SGM_OK) return rc;
+    const int H = e->p.height, W = e->p.width;
+    pack_rows(e->h_in[0], left, ls, H, W);
+    pack_rows(e->h_in[1], right, rs, H, W);
+    if (sky_l) pack_rows(e->h_sky[0], sky_l, sls, e->ih, e->iw);
+    if (sky_r) pack_rows(e->h_sky[1], sky_r, srs, e->ih, e->iw);
+    e->staged_sky[0] = sky_l != nullptr;
+    e->staged_sky[1] = sky_r != nullptr;
+    return SGM_OK;
+}
+
+int engine_launch_staged(sgm_engine* e) {
+    if (!e) return SGM_ERR_INVALID;
+    if (e->busy) return fail(e, SGM_ERR_STATE, "a frame is already in flight on this handle: call sgm_wait first");
+    CU_TRY(e, cudaSetDevice(e->p.device));
+    const size_t HW = (size_t)e->p.height * e->p.width;
+    cudaStream_t st = e->stream;
+    cudaEventRecord(e->ev[SGM_STAGE_UPLOAD], st);
+    CU_TRY(e, cudaMemcpyAsync(e->d_in[0], e->h_in[0], HW, cudaMemcpyHostToDevice, st));
+    CU_TRY(e, cudaMemcpyAsync(e->d_in[1], e->h_in[1], HW, cudaMemcpyHostToDevice, st));
+    for (int v = 0; v < 2; ++v)
+        if (e->staged_sky[v]) CU_TRY(e, cudaMemcpyAsync(e->d_sky[v], e->h_sky[v], e->n, cudaMemcpyHostToDevice, st));
+    LaunchCounter lc;
+    lc.stream = st;
+    lc.sync_each = debug_sync();
+    int rc = run_frame(e, e->d_in[0], e->p.width, e->d_in[1], e->p.width, e->staged_sky[0] ? e->d_sky[0] : nullptr,
+                       e->staged_sky[1] ? e->d_sky[1] : nullptr, lc);
+    e->launches = lc.launches;
+    if (rc != SGM_OK) return abandon_frame(e, rc);
+    cudaError_t c = cudaMemcpyAsync(e->h_final, e->d_final, e->n * sizeof(float), cudaMemcpyDeviceToHost, st);
+    if (c == cudaSuccess && e->host_taps) {
+        // the integer and right-view results the reference keeps in its protected Mats (inc/Solver.h:43-46), narrowed on the device
+        launch_narrow_disp(e->d_disp, e->d_disp8, (int)(e->views * e->n), st, lc);
+        c = lc.err;
+        if (c == cudaSuccess) c = cudaMemcpyAsync(e->h_disp8, e->d_disp8, e->views * e->n, cudaMemcpyDeviceToHost, st);
+        if (c == cudaSuccess && e->views == 2)
+            c = cudaMemcpyAsync(e->h_sub_r, e->d_sub + e->n, e->n * sizeof(float), cudaMemcpyDeviceToHost, st);
+        e->launches = lc.launches;
+    }
+    if (c != cudaSuccess) return abandon_frame(e, fail(e, SGM_ERR_CUDA, "result download: %s", cudaGetErrorString(c)));
+    cudaEventRecord(e->ev[SGM_STAGE_COUNT], st);
+    cudaEventRecord(e->ev_done, st);
+    e->busy = true;
+    e->result_on_host = true;
+    return SGM_OK;
+}
+
+int engine_wait_blocking(sgm_engine* e) {
+    if (!e) return SGM_ERR_INVALID;
+    if (!e->busy) return SGM_OK;
+    CU_TRY(e, cudaSetDevice(e->p.device));
+    cudaError_t c = cudaEventSynchronize(e->ev_done);          // sleeps instead of spinning
+    if (c == cudaSuccess) c = cudaStreamSynchronize(e->stream);  // already drained: returns at once
+    return finish_frame(e, c);
+}
+
+const float* engine_host_result(const sgm_engine* e) { return (e && e->have_result && e->result_on_host) ? e->h_final : nullptr; }
+
+}  // namespace sgmb200
 
 extern "C" {
 
 int sgm_enqueue(sgm_engine* e, const uint8_t* left, size_t ls, const uint8_t* right, size_t rs, const uint8_t* sky_l, size_t sls,
                 const uint8_t* sky_r, size_t srs) {
-    int rc = check_images(e, left, ls, right, rs, sky_l, sls, sky_r, srs);
+    int rc = engine_stage(e, left, ls, right, rs, sky_l, sls, sky_r, srs);
     if (rc != SGM_OK) return rc;
-    CU_TRY(e, cudaSetDevice(e->p.device));
-    const int H = e->p.height, W = e->p.width;
-    cudaStream_t st = e->stream;
-    // pinned staging, then async H2D on the engine's stream
-    pack_rows(e->h_in[0], left, ls, H, W);
-    pack_rows(e->h_in[1], right, rs, H, W);
-    if (sky_l) pack_rows(e->h_sky[0], sky_l, sls, e->ih, e->iw);
-    if (sky_r) pack_rows(e->h_sky[1], sky_r, srs, e->ih, e->iw);
-    cudaEventRecord(e->ev[SGM_STAGE_UPLOAD], st);
-    CU_TRY(e, cudaMemcpyAsync(e->d_in[0], e->h_in[0], (size_t)H * W, cudaMemcpyHostToDevice, st));
-    CU_TRY(e, cudaMemcpyAsync(e->d_in[1], e->h_in[1], (size_t)H * W, cudaMemcpyHostToDevice, st));
-    if (sky_l) CU_TRY(e, cudaMemcpyAsync(e->d_sky[0], e->h_sky[0], e->n, cudaMemcpyHostToDevice, st));
-    if (sky_r) CU_TRY(e, cudaMemcpyAsync(e->d_sky[1], e->h_sky[1], e->n, cudaMemcpyHostToDevice, st));
-    LaunchCounter lc;
-    lc.stream = st;
-    lc.sync_each = std::getenv("SGM_B200_DEBUG_SYNC") != nullptr;
-    e->last_left = e->d_in[0];
-    e->last_left_stride = W;
-    rc = run_frame(e, e->d_in[0], W, e->d_in[1], W, sky_l ? e->d_sky[0] : nullptr, sky_r ? e->d_sky[1] : nullptr, lc);
-    e->launches = lc.launches;
-    if (rc != SGM_OK) return rc;
-    CU_TRY(e, cudaMemcpyAsync(e->h_final, e->d_final, e->n * sizeof(float), cudaMemcpyDeviceToHost, st));
-    cudaEventRecord(e->ev[SGM_STAGE_COUNT], st);
-    e->busy = true;
-    e->result_on_host = true;
-    return SGM_OK;
+    return engine_launch_staged(e);
 }
 
 int sgm_enqueue_device(sgm_engine* e, const void* left, size_t ls, const void* right, size_t rs, const void* sky_l, size_t sls,
@@ -451,15 +497,18 @@ int sgm_enqueue_device(sgm_engine* e, const void* left, size_t ls, const void* r
         CU_TRY(e, cudaMemcpy2DAsync(e->d_sky[1], e->iw, sr, srs, e->iw, e->ih, cudaMemcpyDeviceToDevice, st));
         sr = e->d_sky[1];
     }
+    // The left image is read again after the frame (sgm_point_cloud takes its grey values): keep an engine-owned copy, so
+    // the caller may release or overwrite its buffer as soon as sgm_wait has returned.
+    const size_t W = (size_t)e->p.width;
+    CU_TRY(e, cudaMemcpy2DAsync(e->d_in[0], W, left, ls, W, (size_t)e->p.height, cudaMemcpyDeviceToDevice, st));
     LaunchCounter lc;
     lc.stream = st;
-    lc.sync_each = std::getenv("SGM_B200_DEBUG_SYNC") != nullptr;
-    e->last_left = static_cast<const uint8_t*>(left);
-    e->last_left_stride = ls;
-    rc = run_frame(e, static_cast<const uint8_t*>(left), ls, static_cast<const uint8_t*>(right), rs, sl, sr, lc);
+    lc.sync_each = debug_sync();
+    rc = run_frame(e, e->d_in[0], W, static_cast<const uint8_t*>(right), rs, sl, sr, lc);
     e->launches = lc.launches;
-    if (rc != SGM_OK) return rc;
+    if (rc != SGM_OK) return abandon_frame(e, rc);
     cudaEventRecord(e->ev[SGM_STAGE_COUNT], st);
+    cudaEventRecord(e->ev_done, st);
     e->busy = true;
     e->result_on_host = false;
     return SGM_OK;
@@ -470,24 +519,7 @@ int sgm_wait(sgm_engine* e) {
     if (!e->busy) return SGM_OK;
     CU_TRY(e, cudaSetDevice(e->p.device));
     cudaError_t c = cudaStreamSynchronize(e->stream);
-    e->busy = false;
-    if (c != cudaSuccess) return fail(e, SGM_ERR_CUDA, "frame failed: %s", cudaGetErrorString(c));
-    if (e->h_error && *e->h_error) {
-        *e->h_error = 0;
-        cudaMemset(e->d_error, 0, sizeof(int));
-        return fail(e, SGM_ERR_CUDA, "fused aggregation: a cross-block wait timed out (blocks not co-resident?)");
-    }
-    e->have_result = true;
-    if (e->timing) {
-        for (int k = 0; k < SGM_STAGE_COUNT; ++k) {
-            float ms = 0.f;
-            const int nxt = k + 1 == SGM_STAGE_COUNT ? SGM_STAGE_COUNT : k + 1;
-            if (cudaEventElapsedTime(&ms, e->ev[k], e->ev[nxt]) != cudaSuccess) ms = -1.f;
-            e->stage_ms[k] = ms;
-        }
-        (void)cudaGetLastError();
-    }
-    return SGM_OK;
+    return finish_frame(e, c);
 }
 
 int sgm_process(sgm_engine* e, const uint8_t* left, size_t ls, const uint8_t* right, size_t rs, const uint8_t* sky_l, size_t sls,
@@ -533,16 +565,31 @@ int sgm_get_disparity_u16(sgm_engine* e, int view, uint16_t* dst, size_t dst_str
 int sgm_get_disparity_u8(sgm_engine* e, int view, uint8_t* dst, size_t dst_stride) {
     int rc = ready(e);
     if (rc != SGM_OK) return rc;
-    if (e->D > 128) return fail(e, SGM_ERR_UNSUPPORTED, "8-bit disparity needs max_disp <= 128 (invalid = D+1 must fit a byte)");
     if (!dst || dst_stride < (size_t)e->iw || view < 0 || view >= e->views) return fail(e, SGM_ERR_INVALID, "bad destination / view");
-    uint16_t* tmp = static_cast<uint16_t*>(std::malloc(e->n * sizeof(uint16_t)));
-    if (!tmp) return fail(e, SGM_ERR_NOMEM, "out of host memory");
-    cudaError_t c = cudaMemcpy(tmp, e->d_disp + (size_t)view * e->n, e->n * sizeof(uint16_t), cudaMemcpyDeviceToHost);
-    if (c == cudaSuccess)
+    if (e->host_taps && e->result_on_host) {  // already on the host: narrowed on the device, copied with the result
+        // D = 256: the byte saturates at 255 (the reference's uchar Mats cannot hold D+1 = 257 either, src/Solver.cpp:16-19)
+        for (int r = 0; r < e->ih; ++r) std::memcpy(dst + (size_t)r * dst_stride, e->h_disp8 + (size_t)view * e->n + (size_t)r * e->iw, e->iw);
+        return SGM_OK;
+    }
+    if (e->D > 128) return fail(e, SGM_ERR_UNSUPPORTED, "8-bit disparity needs max_disp <= 128 (invalid = D+1 must fit a byte) or SGM_FLAG_HOST_TAPS (saturating)");
+    std::vector<uint16_t> tmp(e->n);
+    CU_TRY(e, cudaMemcpy(tmp.data(), e->d_disp + (size_t)view * e->n, e->n * sizeof(uint16_t), cudaMemcpyDeviceToHost));
+    for (int r = 0; r < e->ih; ++r)
+        for (int k = 0; k < e->iw; ++k) dst[(size_t)r * dst_stride + k] = (uint8_t)tmp[(size_t)r * e->iw + k];  // uchar Mat, src/Solver.cpp:18-19
+    return SGM_OK;
+}
+
+int sgm_get_subpixel_beta(sgm_engine* e, float* dst, size_t dst_stride) {
+    int rc = ready(e);
+    if (rc != SGM_OK) return rc;
+    if (!dst || dst_stride < e->iw * sizeof(float)) return fail(e, SGM_ERR_INVALID, "bad destination");
+    if (e->views < 2) return fail(e, SGM_ERR_STATE, "this mode has no right view");
+    if (e->host_taps && e->result_on_host) {
         for (int r = 0; r < e->ih; ++r)
-            for (int k = 0; k < e->iw; ++k) dst[(size_t)r * dst_stride + k] = (uint8_t)tmp[(size_t)r * e->iw + k];  // uchar Mat, src/Solver.cpp:18-19
-    std::free(tmp);
-    if (c != cudaSuccess) return fail(e, SGM_ERR_CUDA, "cudaMemcpy: %s", cudaGetErrorString(c));
+            std::memcpy(reinterpret_cast<char*>(dst) + (size_t)r * dst_stride, e->h_sub_r + (size_t)r * e->iw, e->iw * sizeof(float));
+        return SGM_OK;
+    }
+    CU_TRY(e, cudaMemcpy2D(dst, dst_stride, e->d_sub + e->n, e->iw * sizeof(float), e->iw * sizeof(float), e->ih, cudaMemcpyDeviceToHost));
     return SGM_OK;
 }
 
@@ -635,7 +682,6 @@ int sgm_point_cloud(sgm_engine* e, const sgm_camera* cam, double* xyz, uint8_t* 
     int rc = ready(e);
     if (rc != SGM_OK) return rc;
     if (!cam || !count) return fail(e, SGM_ERR_INVALID, "camera / count is null");
-    if (!e->last_left) return fail(e, SGM_ERR_STATE, "no frame has been processed yet");
     const int nb = cloud_blocks((int)e->n);
     if (!e->d_pc_counts) {
         CU_TRY(e, dev_alloc(e, &e->d_pc_counts, (size_t)nb));
@@ -645,7 +691,7 @@ int sgm_point_cloud(sgm_engine* e, const sgm_camera* cam, double* xyz, uint8_t* 
     }
     LaunchCounter lc;
     lc.stream = e->stream;
-    launch_point_cloud(e->d_final, e->last_left, e->last_left_stride, e->ih, e->iw, cam->fx, cam->fy, cam->cx, cam->cy, cam->baseline,
+    launch_point_cloud(e->d_final, e->d_in[0], (size_t)e->p.width, e->ih, e->iw, cam->fx, cam->fy, cam->cx, cam->cy, cam->baseline,
                        cam->max_range, (float)(e->D + 1), e->p.scale, e->d_pc_counts, e->d_pc_offsets, e->d_pc_xyz, e->d_pc_int, (int)e->n,
                        e->stream, lc);
     if (lc.err != cudaSuccess) return fail(e, SGM_ERR_CUDA, "point cloud: %s", cudaGetErrorString(lc.err));

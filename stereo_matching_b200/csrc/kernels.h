@@ -97,6 +97,8 @@ void launch_speckle(const float* f_in, float* f_out, int* labels, int* area, int
 // Solver::show_disp + colormap (src/Solver.cpp:55-93, :652-707): out is a dense (2*h) x w x 3 BGR image.
 void launch_debug_view(const uint8_t* gray, const float* disp, uint8_t* out, int h, int w, int max_disp, cudaStream_t st,
                        LaunchCounter& lc);
+// uint16 disparities -> the reference's CV_8UC1 Mats (inc/Solver.h:43), saturating at 255.
+void launch_narrow_disp(const uint16_t* disp, uint8_t* out, int n, cudaStream_t st, LaunchCounter& lc);
 // node.cpp:119-143: ordered list of camera-frame points (xyz doubles) + grey values; counts / offsets are scratch of
 // cloud_blocks(h*w) and cloud_blocks(h*w) + 1 ints, offsets[cloud_blocks] receives the number of points.
 int cloud_blocks(int n);

@@ -144,7 +144,18 @@ __global__ void cloud_scatter_kernel(const float* __restrict__ disp, const uint8
     }
 }
 
+// Solver::disp / disp_beta are CV_8UC1 (inc/Solver.h:43): the engine's uint16 disparities narrowed for the host shells.
+__global__ void narrow_disp_kernel(const uint16_t* __restrict__ disp, uint8_t* __restrict__ out, int n) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) out[p] = (uint8_t)min((int)disp[p], 255);
+}
+
 }  // namespace
+
+void launch_narrow_disp(const uint16_t* disp, uint8_t* out, int n, cudaStream_t st, LaunchCounter& lc) {
+    narrow_disp_kernel<<<(n + 255) / 256, 256, 0, st>>>(disp, out, n);
+    lc.note("narrow_disp_kernel");
+}
 
 void launch_debug_view(const uint8_t* gray, const float* disp, uint8_t* out, int h, int w, int max_disp, cudaStream_t st, LaunchCounter& lc) {
     dim3 grid((w + 255) / 256, 2 * h);

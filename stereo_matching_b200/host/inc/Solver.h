@@ -72,6 +72,7 @@ protected:
     Mat sky_mask, sky_mask_beta;    // masks handed to the last 4-argument process() (kept between frames like the reference)
 
     sgm_engine *engine;             // the device pipeline (NULL until a derived constructor called open_engine)
+    bool two_views;                 // the pipeline also computes the right ("beta") view (SGM; BM is left-only)
 
 protected:
     // Creates the device pipeline for `algo` (sgm_algo) with the constants above; called once by SGM / BM constructors.

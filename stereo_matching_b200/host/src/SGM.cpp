@@ -12,9 +12,7 @@ SGM::~SGM() {}
 
 void SGM::process(Mat &img_l, Mat &img_r)
 {
-    run_engine(img_l, img_r);
-    // right-view sub-pixel disparity, which the reference leaves in filtered_disp_beta (src/SGM.cpp:801)
-    sgm_get_tap(engine, SGM_TAP_SUBPIXEL, 1, filtered_disp_beta.ptr<float>(0), sgm_tap_bytes(engine, SGM_TAP_SUBPIXEL));
+    run_engine(img_l, img_r);  // also refreshes disp_beta / filtered_disp_beta (src/SGM.cpp:801)
 }
 
 void SGM::process(Mat &img_l, Mat &img_r, Mat &sky_mask, Mat &sky_mask_beta)

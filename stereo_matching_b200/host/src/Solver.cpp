@@ -22,7 +22,7 @@ void die(const char *what, const sgm_engine *e)
 }  // namespace
 
 Solver::Solver(int h, int w, int s, int d)
-    : img_h(0), img_w(0), scale(s), max_disp(d), invalid_disp(d + 1), engine(nullptr)
+    : img_h(0), img_w(0), scale(s), max_disp(d), invalid_disp(d + 1), engine(nullptr), two_views(false)
 {
     // same domain as the reference (src/Solver.cpp:6-10); d == 256 is the engine's widened mode (uint16 disparities
     // inside, the CV_8UC1 `disp` Mats then saturate, get_disp() stays exact)
@@ -67,6 +67,8 @@ void Solver::open_engine(int algo, int paths, int full_h, int full_w)
         p.box_w = p.box_h = scale;
         p.flags |= SGM_FLAG_INTEGER;
     }
+    p.flags |= SGM_FLAG_HOST_TAPS;  // disp / disp_beta / filtered_disp_beta follow the result to pinned host memory
+    two_views = algo != SGM_ALGO_BM;
     if (sgm_create(&engine, &p) != SGM_OK) die("cannot create the device pipeline (no CPU path exists)", nullptr);
 }
 
@@ -81,30 +83,32 @@ void Solver::run_engine(Mat &l, Mat &r)
     }
     img_l = l;  // header copies: the debug view reads the left image later (src/SGM.cpp:59-60)
     img_r = r;
-    const bool sky_l = !sky_mask.empty() && sky_mask.rows == img_h && sky_mask.cols == img_w;
-    const bool sky_r = !sky_mask_beta.empty() && sky_mask_beta.rows == img_h && sky_mask_beta.cols == img_w;
-    if (sky_l || sky_r)
-        std::printf("sky mask found\n");  // src/Solver.cpp:148
-    else
-        std::printf("no sky mask\n");     // src/Solver.cpp:151
-    if (sgm_process(engine, l.ptr<uchar>(0), l.step, r.ptr<uchar>(0), r.step, sky_l ? sky_mask.ptr<uchar>(0) : nullptr,
-                    sky_l ? (size_t)sky_mask.step : 0, sky_r ? sky_mask_beta.ptr<uchar>(0) : nullptr,
-                    sky_r ? (size_t)sky_mask_beta.step : 0) != SGM_OK)
+    // src/Solver.cpp:146-152 prints per view; a mask that is present must be a CV_8UC1 image of the working size (the
+    // reference would index it as one): anything else is misuse and ends like the other argument checks, loudly
+    const Mat *masks[2] = {&sky_mask, &sky_mask_beta};
+    bool have[2];
+    for (int v = 0; v < 2; ++v) {
+        have[v] = !masks[v]->empty();
+        if (have[v] && (masks[v]->rows != img_h || masks[v]->cols != img_w || masks[v]->type() != CV_8UC1)) {
+            std::fprintf(stderr, "stereo_matching_b200: process(): sky mask %d must be CV_8UC1, %d x %d (got %d x %d)\n", v, img_w, img_h,
+                         masks[v]->cols, masks[v]->rows);
+            std::abort();
+        }
+        std::printf(have[v] ? "sky mask found\n" : "no sky mask\n");
+    }
+    if (sgm_process(engine, l.ptr<uchar>(0), l.step, r.ptr<uchar>(0), r.step, have[0] ? sky_mask.ptr<uchar>(0) : nullptr,
+                    have[0] ? (size_t)sky_mask.step : 0, have[1] ? sky_mask_beta.ptr<uchar>(0) : nullptr,
+                    have[1] ? (size_t)sky_mask_beta.step : 0) != SGM_OK)
         die("process() failed", engine);
 
+    // Results: all of them reached pinned host memory on the frame's stream (SGM_FLAG_HOST_TAPS), the 8-bit disparities
+    // already narrowed on the device; what is left is one row-wise copy each into the Mats (which may be pitched).
     if (sgm_get_disparity_f32(engine, filtered_disp.ptr<float>(0), filtered_disp.step) != SGM_OK) die("get_disp", engine);
-    // the integer and right-view results the reference keeps in its protected Mats
-    std::vector<uint16_t> d16((size_t)img_h * img_w);
-    for (int view = 0; view < 2; ++view) {
-        Mat &dst = view == 0 ? disp : disp_beta;
-        if (sgm_get_disparity_u16(engine, view, d16.data(), (size_t)img_w * sizeof(uint16_t)) != SGM_OK) break;  // BM has one view
-        for (int i = 0; i < img_h; ++i) {
-            uchar *row = dst.ptr<uchar>(i);
-            for (int j = 0; j < img_w; ++j) {
-                const unsigned v = d16[(size_t)i * img_w + j];
-                row[j] = (uchar)(v > 255 ? 255 : v);
-            }
-        }
+    if (sgm_get_disparity_u8(engine, 0, disp.ptr<uchar>(0), disp.step) != SGM_OK) die("disp", engine);
+    if (two_views) {
+        if (sgm_get_disparity_u8(engine, 1, disp_beta.ptr<uchar>(0), disp_beta.step) != SGM_OK) die("disp_beta", engine);
+        // right-view sub-pixel disparity, which the reference leaves in filtered_disp_beta (src/SGM.cpp:801)
+        if (sgm_get_subpixel_beta(engine, filtered_disp_beta.ptr<float>(0), filtered_disp_beta.step) != SGM_OK) die("filtered_disp_beta", engine);
     }
     // the masks stay set until the next 4-argument process(), as in the reference (src/SGM.cpp:831-833)
 }
