@@ -180,6 +180,22 @@ typedef struct sgm_camera {
 } sgm_camera;
 SGM_API int sgm_point_cloud(sgm_engine* e, const sgm_camera* cam, double* xyz, uint8_t* intensity, size_t capacity, size_t* count);
 
+/* No counterpart in the reference: added for callers that must not allocate (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The speckle filter of Solver::post_filter
+ * (src/Solver.cpp:514-566 as called at :634: 4-connected components under |a - b| < max_dis; components of at most max_size
+ * pixels become invalid_value) on a caller-owned DEVICE image, queued on `stream` (a cudaStream_t; NULL = the default stream)
+ * of `device`; the call returns once the four kernels are queued.  in and out are height x width dense float32 device
+ * buffers and may be the same buffer.  The label / area scratch is a static 16 MiB __device__ array inside the library
+ * (held by every GPU that loads it), so the call performs no cudaMalloc / cudaFree / allocating library call; images of more
+ * than SGM_SPECKLE_STATIC_MAX_PIXELS pixels are rejected with SGM_ERR_UNSUPPORTED.  All calls on a device SHARE that array:
+ * calls that overlap on the GPU (different streams, different threads) race and give wrong results — keep them on one stream
+ * or order them with events.  Nothing has to be cleared between calls (the first kernel rewrites what the later ones read).
+ * The first call per device looks the array's address up (cudaGetSymbolAddress): make it outside graph capture.
+ * Same result, bit for bit, as the speckle stage of sgm_process (SGM_TAP_MEDIAN -> SGM_TAP_FINAL). */
+#define SGM_SPECKLE_STATIC_MAX_PIXELS (1 << 21)
+SGM_API int sgm_speckle_filter_static(int device, const float* in_device, float* out_device, int height, int width, float invalid_value,
+                                      int max_size, float max_dis, void* stream);
+
 SGM_API int sgm_abi_version(void);
 
 #ifdef __cplusplus

@@ -25,7 +25,7 @@ EXPORTS = [
     "sgm_wait", "sgm_enqueue_device", "sgm_get_disparity_f32", "sgm_get_disparity_u8", "sgm_get_disparity_u16",
     "sgm_disparity_device", "sgm_tap_bytes", "sgm_get_tap", "sgm_get_size", "sgm_get_launch_count", "sgm_get_stage_ms",
     "sgm_get_stream", "sgm_device_bytes", "sgm_cost_volume_sad", "sgm_render_debug_view", "sgm_point_cloud",
-    "sgm_get_subpixel_beta",
+    "sgm_get_subpixel_beta", "sgm_speckle_filter_static",
 ]
 
 
@@ -87,6 +87,7 @@ def lib():
         L.sgm_device_bytes.argtypes = [vp]
         L.sgm_device_bytes.restype = sz
         L.sgm_cost_volume_sad.argtypes = [i, vp, vp, i, i, i, i, i, i, vp]
+        L.sgm_speckle_filter_static.argtypes = [i, vp, vp, i, i, C.c_float, i, C.c_float, vp]
         L.sgm_render_debug_view.argtypes = [vp, vp, sz]
         L.sgm_point_cloud.argtypes = [vp, C.POINTER(Camera), C.POINTER(C.c_double), vp, sz, C.POINTER(sz)]
         _lib = L
@@ -258,6 +259,17 @@ class BM(Solver):
 class BMSad(Solver):
     """SAD block matching (BASELINE.json config 2), built from the reference's SAD() (src/cost.cpp:4-30)."""
     algo = ALGO_BM_SAD
+
+
+SPECKLE_STATIC_MAX_PIXELS = 1 << 21
+
+
+def speckle_filter_static(in_ptr, out_ptr, h, w, invalid_value, max_size=1000, max_dis=2.0, device=0, stream=None) -> None:
+    """sgm_speckle_filter_static: the speckle stage on caller-owned DEVICE buffers (raw pointers), no allocation; queued on
+    `stream` (None = default stream), not synchronised."""
+    rc = lib().sgm_speckle_filter_static(device, in_ptr, out_ptr, h, w, invalid_value, max_size, max_dis, stream)
+    if rc != 0:
+        raise SgmError(rc, lib().sgm_last_error(None).decode())
 
 
 def cost_volume_sad(left, right, max_disp, win_h, win_w, scale=1, device=0) -> np.ndarray:

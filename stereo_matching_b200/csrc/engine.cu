@@ -705,6 +705,23 @@ int sgm_point_cloud(sgm_engine* e, const sgm_camera* cam, double* xyz, uint8_t* 
     return SGM_OK;
 }
 
+int sgm_speckle_filter_static(int device, const float* in_device, float* out_device, int height, int width, float invalid_value,
+                              int max_size, float max_dis, void* stream) {
+    static_assert(SPECKLE_STATIC_MAX_PIXELS == SGM_SPECKLE_STATIC_MAX_PIXELS, "header and kernels disagree on the static scratch size");
+    if (!in_device || !out_device || height <= 0 || width <= 0 || max_size < 0)
+        return fail(nullptr, SGM_ERR_INVALID, "sgm_speckle_filter_static: bad argument");
+    if ((size_t)height * (size_t)width > (size_t)SGM_SPECKLE_STATIC_MAX_PIXELS)
+        return fail(nullptr, SGM_ERR_UNSUPPORTED, "sgm_speckle_filter_static: %d x %d = %zu pixels exceed the static scratch (%d pixels); use sgm_process",
+                    width, height, (size_t)height * (size_t)width, (int)SGM_SPECKLE_STATIC_MAX_PIXELS);
+    if (cudaSetDevice(device) != cudaSuccess) return fail(nullptr, SGM_ERR_CUDA, "no CUDA device %d: this engine has no CPU path", device);
+    LaunchCounter lc;
+    lc.stream = static_cast<cudaStream_t>(stream);
+    cudaError_t c = launch_speckle_static(device, in_device, out_device, height, width, invalid_value, max_size, max_dis, lc.stream, lc);
+    if (c != cudaSuccess)
+        return fail(nullptr, SGM_ERR_CUDA, "sgm_speckle_filter_static: %s failed: %s", lc.failed ? lc.failed : "set-up", cudaGetErrorString(c));
+    return SGM_OK;
+}
+
 int sgm_cost_volume_sad(int device, const uint8_t* left, const uint8_t* right, int height, int width, int max_disp, int win_h, int win_w,
                         int scale, float* out) {
     if (!left || !right || !out || height <= 0 || width <= 0 || max_disp <= 0 || scale <= 0 || win_h <= 0 || win_w <= 0)

@@ -93,6 +93,12 @@ void launch_median_fill(const float* src, float* f, int h, int w, int d, int win
 void launch_speckle(const float* f_in, float* f_out, int* labels, int* area, int h, int w, float value, int max_size,
                     float max_dis, cudaStream_t st, LaunchCounter& lc);
 
+// The same filter with labels / area in a file-scope static __device__ array of post_kernels.cu instead of caller scratch
+// (sgm_speckle_filter_static: no allocation anywhere).  `device` must be the current device; h * w <= SPECKLE_STATIC_MAX_PIXELS.
+constexpr int SPECKLE_STATIC_MAX_PIXELS = 1 << 21;  // == SGM_SPECKLE_STATIC_MAX_PIXELS of include/sgm_b200.h (1920x1080 fits)
+cudaError_t launch_speckle_static(int device, const float* f_in, float* f_out, int h, int w, float value, int max_size, float max_dis,
+                                  cudaStream_t st, LaunchCounter& lc);
+
 // ---- consumers of the result (view_kernels.cu) ---------------------------------------------------
 // Solver::show_disp + colormap (src/Solver.cpp:55-93, :652-707): out is a dense (2*h) x w x 3 BGR image.
 void launch_debug_view(const uint8_t* gray, const float* disp, uint8_t* out, int h, int w, int max_disp, cudaStream_t st,

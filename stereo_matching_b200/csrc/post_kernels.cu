@@ -3,6 +3,7 @@
 // Replaces src/SGM.cpp:803-818 and Solver::post_filter (src/Solver.cpp:600-635, speckle_filter_new
 // :514-566) of the reference, with the reference's serial (single-thread) semantics.
 #include <cstdlib>
+#include <mutex>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -10,6 +11,12 @@
 namespace sgmb200 {
 
 namespace {
+
+// Scratch of the allocation-free speckle entry point (sgm_speckle_filter_static): labels [MAX] then areas [MAX], 16 MiB.
+// It lives in the module image: every GPU that loads the library holds it until the process exits.  In HOST code this
+// name is only a stand-in for the symbol, never a device address: speckle_static_scratch() below asks the runtime for the
+// address (cudaGetSymbolAddress, once per device) and the launcher passes that pointer to the kernels.
+static __device__ __align__(256) int g_speckle_static_scratch[2 * (size_t)SPECKLE_STATIC_MAX_PIXELS];
 
 // src/SGM.cpp:803-818: for j >= dl: dr = right(i, int(j - dl/scale)); |dl - dr| > thresh -> dl = D+1.
 // Writes the result twice: `out_keep` (the LR tap) and `out_work` (the buffer the median updates in place).
@@ -488,6 +495,39 @@ void launch_speckle(const float* f, float* f_out, int* labels, int* area, int h,
     lc.note("speckle_count_kernel");
     speckle_apply_kernel<<<(n + 255) / 256, 256, 0, st>>>(f, f_out, labels, area, n, value, max_size);
     lc.note("speckle_apply_kernel");
+}
+
+// Device address of g_speckle_static_scratch on the CURRENT device (which must be `device`), looked up once per device.
+static cudaError_t speckle_static_scratch(int device, int** out) {
+    constexpr int MAX_DEVICES = 64;
+    static std::mutex mu;
+    static int* cached[MAX_DEVICES] = {};
+    if (device < 0 || device >= MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!cached[device]) {
+        int cur = -1;
+        cudaError_t c = cudaGetDevice(&cur);
+        if (c != cudaSuccess) return c;
+        if (cur != device) return cudaErrorInvalidDevice;
+        void* ptr = nullptr;
+        c = cudaGetSymbolAddress(&ptr, g_speckle_static_scratch);
+        if (c != cudaSuccess) return c;
+        cached[device] = static_cast<int*>(ptr);
+    }
+    *out = cached[device];
+    return cudaSuccess;
+}
+
+cudaError_t launch_speckle_static(int device, const float* f, float* f_out, int h, int w, float value, int max_size, float max_dis,
+                                  cudaStream_t st, LaunchCounter& lc) {
+    if ((size_t)h * w > (size_t)SPECKLE_STATIC_MAX_PIXELS) return cudaErrorInvalidValue;
+    int* scratch = nullptr;
+    cudaError_t c = speckle_static_scratch(device, &scratch);
+    if (c != cudaSuccess) return c;
+    // nothing to clear: speckle_rows_kernel writes every label and zeroes every area count of the h * w pixels before the
+    // later passes read them, so what the previous call left in the array is never seen
+    launch_speckle(f, f_out, scratch, scratch + SPECKLE_STATIC_MAX_PIXELS, h, w, value, max_size, max_dis, st, lc);
+    return lc.err;
 }
 
 }  // namespace sgmb200
