@@ -162,6 +162,13 @@ SGM_API size_t sgm_device_bytes(const sgm_engine* e);
  * out is a host float volume [ih][iw][D], as Solver::build_dsi (src/Solver.cpp:96-117) would fill it. */
 SGM_API int sgm_cost_volume_sad(int device, const uint8_t* left, const uint8_t* right, int height, int width, int max_disp,
                         int win_h, int win_w, int scale, float* out);
+/* SSD (src/cost.cpp:33-59): sum of squared differences / win_h / win_w; windows up to 258 pixels (exact float accumulation). */
+SGM_API int sgm_cost_volume_ssd(int device, const uint8_t* left, const uint8_t* right, int height, int width, int max_disp,
+                        int win_h, int win_w, int scale, float* out);
+/* CT (src/cost.cpp:62-96): per-disparity census + Hamming distance with the function's own conventions (right centre pixel at
+ * x - d unscaled, taps with x_r < 0 dropped); windows up to 64 pixels. */
+SGM_API int sgm_cost_volume_ct(int device, const uint8_t* left, const uint8_t* right, int height, int width, int max_disp,
+                       int win_h, int win_w, int scale, float* out);
 
 /* Solver::show_disp(debug_view) (src/Solver.cpp:55-93) with Solver::colormap (:652-707), rendered on the device from the
  * last frame: dst is a (2 * height/scale) x (width/scale) 8-bit BGR image (3 bytes per pixel, dst_stride bytes per row):
@@ -179,6 +186,37 @@ typedef struct sgm_camera {
     float max_range;        /* node.cpp:117 (100) */
 } sgm_camera;
 SGM_API int sgm_point_cloud(sgm_engine* e, const sgm_camera* cam, double* xyz, uint8_t* intensity, size_t capacity, size_t* count);
+
+/* ---- Frame-stream runner ------------------------------------------------------------------------------------------
+ * The reference's caller (node.cpp:49,93,104) owns ONE Solver and calls process() frame after frame; a Solver keeps no
+ * state between frames (scratch members only), so a stream of stereo pairs shards by frame.  sgm_stream is that loop for
+ * 1..N GPUs of one box behind one handle: frame k goes to device k mod N, every device keeps `inflight` frames in flight
+ * (one engine handle each: own stream, own pinned staging for inputs and result), one host thread per device issues the
+ * launches, and results come back in submission order.  No collective and no peer traffic: inputs and results cross PCIe.
+ *
+ *   sgm_stream_submit  copies the pair (and masks, nullable) into pinned staging and returns; it blocks only while the slot
+ *                      the frame maps to is still occupied (back-pressure: at most n_devices * inflight frames are pending,
+ *                      so a producer that never calls sgm_stream_next stalls there).  *frame_index (nullable) = k.
+ *   sgm_stream_next    blocks until the OLDEST pending frame is done and hands out its final disparity (Solver::get_disp():
+ *                      float32, (height/scale) x (width/scale), invalid = D+1): copied into dst when dst != NULL, and/or as
+ *                      a pointer into the pinned result buffer (*view, dense rows) that stays valid until the next
+ *                      sgm_stream_next / sgm_stream_destroy on this stream, or until n_devices * inflight further frames
+ *                      have been submitted (the slot is then needed again).  Returns SGM_ERR_STATE when nothing is pending.
+ * One producer thread and one consumer thread may call submit and next concurrently; two producers (or two consumers) may not.
+ * A frame that fails reports its error from sgm_stream_next (message: sgm_stream_last_error) and the stream stays usable. */
+typedef struct sgm_stream sgm_stream; /* opaque */
+SGM_API int sgm_stream_create(sgm_stream** out, const sgm_params* params, const int* devices, int n_devices, int inflight);
+SGM_API void sgm_stream_destroy(sgm_stream* s);
+SGM_API int sgm_stream_submit(sgm_stream* s, const uint8_t* left, size_t left_stride, const uint8_t* right, size_t right_stride,
+                              const uint8_t* sky_l, size_t sky_l_stride, const uint8_t* sky_r, size_t sky_r_stride,
+                              uint64_t* frame_index);
+SGM_API int sgm_stream_next(sgm_stream* s, float* dst, size_t dst_stride, const float** view, uint64_t* frame_index);
+/* Frames submitted and not yet handed out by sgm_stream_next. */
+SGM_API int sgm_stream_pending(const sgm_stream* s);
+/* Kernel launches issued so far by all devices of the stream (bench.py's gpu_launches). */
+SGM_API uint64_t sgm_stream_launches(const sgm_stream* s);
+/* With s == NULL: message of the last failed sgm_stream_create on this thread. */
+SGM_API const char* sgm_stream_last_error(const sgm_stream* s);
 
 /* No counterpart in the reference: added for callers that must not allocate (code under
  * CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The speckle filter of Solver::post_filter

@@ -238,6 +238,48 @@ int ref_time_process(int algo, int h, int w, int scale, int d, const uint8_t* le
 // Stage taps: re-runs the protected stages of Solver in the order process() uses them
 // (src/SGM.cpp:66-72 and :449-454) and copies the intermediate buffers out.
 // beta = 0: left-view volume, 1: right-view ("beta") volume.  All outputs nullable.
+// A solver kept across frames, the way node.cpp:49,93 uses it (one make_shared<SGM>, process() per frame): bench.py's reference
+// arm times frame after frame of a stream of DIFFERENT pairs without paying the 2 GB allocation (and its first-touch page
+// faults) per frame.  ref_open -> handle; ref_run -> wall milliseconds of one process() (optionally copies get_disp() out).
+struct RefSession {
+    int algo, h, w, scale, d;
+    Probe<SGM>* sgm = nullptr;
+    Probe<BM>* bm = nullptr;
+};
+void* ref_open(int algo, int h, int w, int scale, int d) {
+    if (algo != 0 && algo != 1) return nullptr;
+    StdoutMute mute;
+    RefSession* s = new RefSession{algo, h, w, scale, d};
+    if (algo == 0)
+        s->sgm = new Probe<SGM>(h, w, scale, d);
+    else
+        s->bm = new Probe<BM>(h, w, scale, d);
+    return s;
+}
+double ref_run(void* session, const uint8_t* left, const uint8_t* right, float* fdisp_out) {
+    RefSession* s = static_cast<RefSession*>(session);
+    if (!s || !left || !right) return -1.0;
+    StdoutMute mute;
+    cv::Mat L(s->h, s->w, CV_8UC1), R(s->h, s->w, CV_8UC1);
+    std::memcpy(L.data, left, (size_t)s->h * s->w);
+    std::memcpy(R.data, right, (size_t)s->h * s->w);
+    auto t0 = std::chrono::steady_clock::now();
+    if (s->sgm)
+        s->sgm->process(L, R);
+    else
+        s->bm->process(L, R);
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    if (fdisp_out) copy_mat_f32(s->sgm ? s->sgm->get_disp() : s->bm->get_disp(), fdisp_out);
+    return ms;
+}
+void ref_close(void* session) {
+    RefSession* s = static_cast<RefSession*>(session);
+    if (!s) return;
+    delete s->sgm;
+    delete s->bm;
+    delete s;
+}
+
 int ref_stages(int algo, int h, int w, int scale, int d, const uint8_t* left, const uint8_t* right, const uint8_t* sky,
                int beta, uint64_t* ct_l, uint64_t* ct_r, float* cost_raw, float* cost_h, float* cost_hv) {
     if (!left || !right) return -1;

@@ -12,21 +12,44 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "_ref", "libsgm_ref.so")
+# the same unmodified sources compiled against a copy of inc/Solver.h with COST_WIN_H = COST_WIN_W = 1 (make -C oracle
+# ref_nofilter): the reference with its cost filter off, the direct pin of the integer / DPX mode's oracle
+LIB_PATH_NOFILTER = os.path.join(_HERE, "_ref", "libsgm_ref_nofilter.so")
 
 _u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
-_lib = None
+_libs = {}
+_variant = "default"
 
 
-def available() -> bool:
-    return os.path.exists(LIB_PATH)
+def _path(variant):
+    return LIB_PATH_NOFILTER if variant == "nofilter" else LIB_PATH
+
+
+def available(variant="default") -> bool:
+    return os.path.exists(_path(variant))
+
+
+class use:
+    """`with refbind.use("nofilter"): ...` routes every call of this module to libsgm_ref_nofilter.so."""
+
+    def __init__(self, variant):
+        self.variant = variant
+
+    def __enter__(self):
+        global _variant
+        self.prev, _variant = _variant, self.variant
+        return self
+
+    def __exit__(self, *exc):
+        global _variant
+        _variant = self.prev
 
 
 def lib():
-    global _lib
-    if _lib is None:
-        if not available():
-            raise RuntimeError(f"{LIB_PATH} missing: run `make -C oracle ref` where /root/reference exists")
-        L = C.CDLL(LIB_PATH)
+    if _variant not in _libs:
+        if not available(_variant):
+            raise RuntimeError(f"{_path(_variant)} missing: run `make -C oracle ref ref_nofilter` where /root/reference exists")
+        L = C.CDLL(_path(_variant))
         L.ref_process.restype = C.c_double
         L.ref_process.argtypes = [C.c_int] * 5 + [C.c_void_p] * 9
         L.ref_time_process.restype = C.c_int
@@ -42,11 +65,17 @@ def lib():
         if hasattr(L, "ref_show_disp"):
             L.ref_show_disp.restype = C.c_int
             L.ref_show_disp.argtypes = [C.c_int] * 5 + [C.c_void_p] * 4
+        if hasattr(L, "ref_open"):
+            L.ref_open.restype = C.c_void_p
+            L.ref_open.argtypes = [C.c_int] * 5
+            L.ref_run.restype = C.c_double
+            L.ref_run.argtypes = [C.c_void_p] * 4
+            L.ref_close.argtypes = [C.c_void_p]
         L.ref_set_threads.argtypes = [C.c_int]
         L.ref_set_quiet.argtypes = [C.c_int]
         L.ref_max_threads.restype = C.c_int
-        _lib = L
-    return _lib
+        _libs[_variant] = L
+    return _libs[_variant]
 
 
 def _p(a):
@@ -111,6 +140,29 @@ def time_process(algo, left, right, scale, d, iters):
     if rc != 0:
         raise RuntimeError("ref_time_process failed")
     return ms
+
+
+class Session:
+    """One reference solver kept across frames (node.cpp:49,93): run(left, right) -> wall ms of process()."""
+
+    def __init__(self, algo, h, w, scale, d):
+        self.shape = (h // scale, w // scale)
+        self._s = lib().ref_open(ALGO[algo], h, w, scale, d)
+        if not self._s:
+            raise RuntimeError("ref_open failed")
+
+    def run(self, left, right, want_disp=False):
+        left, right = _u8(left), _u8(right)
+        out = np.zeros(self.shape, np.float32) if want_disp else None
+        ms = lib().ref_run(self._s, _p(left), _p(right), _p(out))
+        if ms < 0:
+            raise RuntimeError("ref_run failed")
+        return (ms, out) if want_disp else ms
+
+    def close(self):
+        if self._s:
+            lib().ref_close(self._s)
+            self._s = None
 
 
 def stages(algo, left, right, scale, d, beta=False, sky=None):

@@ -183,3 +183,45 @@ def point_cloud(f, left, d, scale, fx, fy, cx, cy, baseline=0.5, max_range=100.0
     xyz = np.stack([X[keep], Y[keep], Z[keep]], axis=1)
     inten = np.asarray(left)[:ih, :iw][keep]
     return xyz, inten
+
+
+def window_cost_volume(kind, left, right, d, win_h, win_w, scale=1) -> np.ndarray:
+    """Dense numpy restatement of SSD (src/cost.cpp:33-59) / CT (:62-96) as Solver::build_dsi (src/Solver.cpp:96-117) would call
+    them for every (pixel, disparity) of the left view -> (h, w, d) float32.  Pinned against the reference's own functions
+    (refbind.cost_volume) in tests/test_oracle_cpu.py.
+      SSD: sum over the window of (L(y, x_l) - R(y, max(x_l - k/scale, 0)))^2 with replicate-clamped (y, x_l), / win_h / win_w.
+      CT : number of window taps (centre skipped, taps with x_r = x_l - k/scale < 0 dropped) whose comparisons against the
+           centre pixels L(y, x) and R(y, max(x - k, 0)) — k NOT divided by scale — disagree."""
+    L = np.ascontiguousarray(left, np.uint8).astype(np.int32)
+    R = np.ascontiguousarray(right, np.uint8).astype(np.int32)
+    h, w = L.shape
+    rh, rw = win_h // 2, win_w // 2
+    ys, xs = np.arange(h), np.arange(w)
+    out = np.zeros((h, w, d), np.float32)
+    for k in range(d):
+        ks = k // scale
+        acc = np.zeros((h, w), np.int64)
+        if kind == "ct":
+            cl = L
+            cr = R[:, np.maximum(xs - k, 0)]
+        for a in range(-rh, rh + 1):
+            y = np.clip(ys + a, 0, h - 1)
+            for b in range(-rw, rw + 1):
+                xl = np.clip(xs + b, 0, w - 1)
+                if kind == "ssd":
+                    xr = np.maximum(xl - ks, 0)
+                    df = L[y][:, xl] - R[y][:, xr]
+                    acc += df * df
+                else:
+                    if a == 0 and b == 0:
+                        continue
+                    xr = xl - ks
+                    keep = xr >= 0
+                    bl = L[y][:, xl] > cl
+                    br = R[y][:, np.maximum(xr, 0)] > cr
+                    acc += (bl != br) & keep[None, :]
+        if kind == "ssd":
+            out[:, :, k] = (acc.astype(np.float32) / np.float32(win_h)) / np.float32(win_w)
+        else:
+            out[:, :, k] = acc.astype(np.float32)
+    return out

@@ -25,7 +25,8 @@ EXPORTS = [
     "sgm_wait", "sgm_enqueue_device", "sgm_get_disparity_f32", "sgm_get_disparity_u8", "sgm_get_disparity_u16",
     "sgm_disparity_device", "sgm_tap_bytes", "sgm_get_tap", "sgm_get_size", "sgm_get_launch_count", "sgm_get_stage_ms",
     "sgm_get_stream", "sgm_device_bytes", "sgm_cost_volume_sad", "sgm_render_debug_view", "sgm_point_cloud",
-    "sgm_get_subpixel_beta", "sgm_speckle_filter_static",
+    "sgm_get_subpixel_beta", "sgm_speckle_filter_static", "sgm_stream_create", "sgm_stream_destroy", "sgm_stream_submit",
+    "sgm_stream_next", "sgm_stream_pending", "sgm_stream_launches", "sgm_stream_last_error", "sgm_cost_volume_ssd", "sgm_cost_volume_ct",
 ]
 
 
@@ -86,8 +87,19 @@ def lib():
         L.sgm_get_stream.restype = vp
         L.sgm_device_bytes.argtypes = [vp]
         L.sgm_device_bytes.restype = sz
-        L.sgm_cost_volume_sad.argtypes = [i, vp, vp, i, i, i, i, i, i, vp]
+        for name in ("sgm_cost_volume_sad", "sgm_cost_volume_ssd", "sgm_cost_volume_ct"):
+            getattr(L, name).argtypes = [i, vp, vp, i, i, i, i, i, i, vp]
         L.sgm_speckle_filter_static.argtypes = [i, vp, vp, i, i, C.c_float, i, C.c_float, vp]
+        L.sgm_stream_create.argtypes = [C.POINTER(vp), C.POINTER(Params), C.POINTER(i), i, i]
+        L.sgm_stream_destroy.argtypes = [vp]
+        L.sgm_stream_destroy.restype = None
+        L.sgm_stream_submit.argtypes = [vp, vp, sz, vp, sz, vp, sz, vp, sz, C.POINTER(C.c_uint64)]
+        L.sgm_stream_next.argtypes = [vp, vp, sz, C.POINTER(vp), C.POINTER(C.c_uint64)]
+        L.sgm_stream_pending.argtypes = [vp]
+        L.sgm_stream_launches.argtypes = [vp]
+        L.sgm_stream_launches.restype = C.c_uint64
+        L.sgm_stream_last_error.argtypes = [vp]
+        L.sgm_stream_last_error.restype = C.c_char_p
         L.sgm_render_debug_view.argtypes = [vp, vp, sz]
         L.sgm_point_cloud.argtypes = [vp, C.POINTER(Camera), C.POINTER(C.c_double), vp, sz, C.POINTER(sz)]
         _lib = L
@@ -261,6 +273,72 @@ class BMSad(Solver):
     algo = ALGO_BM_SAD
 
 
+class Stream:
+    """sgm_stream: frames of one size over `devices` (list of CUDA ordinals), `inflight` frames in flight per device, results
+    in submission order.  submit() blocks only for back-pressure; next() blocks until the oldest pending frame is done."""
+
+    def __init__(self, h, w, s, d, devices=(0,), inflight=4, algo=ALGO_SGM, flags=0, **over):
+        self._h = None
+        self.params = default_params(h, w, s, d, algo, flags=flags, **over)
+        self.img_h, self.img_w = h // s, w // s
+        self.capacity = len(devices) * inflight
+        devs = (C.c_int * len(devices))(*devices)
+        handle = C.c_void_p()
+        rc = lib().sgm_stream_create(C.byref(handle), C.byref(self.params), devs, len(devices), inflight)
+        if rc != 0:
+            raise SgmError(rc, lib().sgm_stream_last_error(None).decode())
+        self._h = handle
+
+    def _check(self, rc):
+        if rc != 0:
+            raise SgmError(rc, lib().sgm_stream_last_error(self._h).decode())
+
+    def close(self):
+        if self._h is not None:
+            lib().sgm_stream_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def submit(self, img_l, img_r, sky_l=None, sky_r=None) -> int:
+        l, r = _img(img_l), _img(img_r)
+        sl = None if sky_l is None else _img(sky_l)
+        sr = None if sky_r is None else _img(sky_r)
+        p = lambda a: None if a is None else a.ctypes.data
+        st = lambda a: 0 if a is None else a.strides[0]
+        k = C.c_uint64()
+        self._check(lib().sgm_stream_submit(self._h, p(l), st(l), p(r), st(r), p(sl), st(sl), p(sr), st(sr), C.byref(k)))
+        return k.value  # the inputs were copied into pinned staging: the arrays may be reused at once
+
+    def next_into(self, out: np.ndarray) -> int:
+        k = C.c_uint64()
+        self._check(lib().sgm_stream_next(self._h, out.ctypes.data, out.strides[0], None, C.byref(k)))
+        return k.value
+
+    def next(self):
+        out = np.empty((self.img_h, self.img_w), np.float32)
+        return self.next_into(out), out
+
+    def next_view(self):
+        """(frame index, zero-copy float32 view of the pinned result); the view dies at the next next*() call."""
+        k, ptr = C.c_uint64(), C.c_void_p()
+        self._check(lib().sgm_stream_next(self._h, None, 0, C.byref(ptr), C.byref(k)))
+        buf = (C.c_float * (self.img_h * self.img_w)).from_address(ptr.value)
+        return k.value, np.frombuffer(buf, np.float32).reshape(self.img_h, self.img_w)
+
+    @property
+    def pending(self) -> int:
+        return lib().sgm_stream_pending(self._h)
+
+    @property
+    def launches(self) -> int:
+        return lib().sgm_stream_launches(self._h)
+
+
 SPECKLE_STATIC_MAX_PIXELS = 1 << 21
 
 
@@ -272,11 +350,17 @@ def speckle_filter_static(in_ptr, out_ptr, h, w, invalid_value, max_size=1000, m
         raise SgmError(rc, lib().sgm_last_error(None).decode())
 
 
-def cost_volume_sad(left, right, max_disp, win_h, win_w, scale=1, device=0) -> np.ndarray:
+def cost_volume(kind, left, right, max_disp, win_h, win_w, scale=1, device=0) -> np.ndarray:
+    """Dense forms of SAD / SSD / CT (inc/cost.h:7-10) as Solver::build_dsi would fill them: (h, w, max_disp) float32."""
+    fn = getattr(lib(), {"sad": "sgm_cost_volume_sad", "ssd": "sgm_cost_volume_ssd", "ct": "sgm_cost_volume_ct"}[kind])
     l, r = np.ascontiguousarray(_img(left)), np.ascontiguousarray(_img(right))
     h, w = l.shape
     out = np.empty((h, w, max_disp), np.float32)
-    rc = lib().sgm_cost_volume_sad(device, l.ctypes.data, r.ctypes.data, h, w, max_disp, win_h, win_w, scale, out.ctypes.data)
+    rc = fn(device, l.ctypes.data, r.ctypes.data, h, w, max_disp, win_h, win_w, scale, out.ctypes.data)
     if rc != 0:
         raise SgmError(rc, lib().sgm_last_error(None).decode())
     return out
+
+
+def cost_volume_sad(left, right, max_disp, win_h, win_w, scale=1, device=0) -> np.ndarray:
+    return cost_volume("sad", left, right, max_disp, win_h, win_w, scale, device)

@@ -337,6 +337,92 @@ __global__ void __launch_bounds__(256) sad_volume_kernel(const uint8_t* __restri
 }
 
 
+// src/cost.cpp:33-59 (SSD) for every (pixel, d): the same separable scheme as sad_volume_kernel with squared differences.
+// The reference accumulates in float; every partial sum is an integer below 2^24 as long as win_h * win_w * 255^2 < 2^24
+// (windows up to 258 pixels; the launcher rejects larger ones), so integer accumulation gives the same float, and the
+// result is sum / win_h / win_w with the reference's two divisions.
+__global__ void __launch_bounds__(256) ssd_volume_kernel(const uint8_t* __restrict__ img_l, const uint8_t* __restrict__ img_r,
+                                                         float* __restrict__ cost, int h, int w, int d, int win_h, int win_w, int scale) {
+    extern __shared__ unsigned vs32[];  // [(SAD_TJ + 2*rw)][d] vertical sums
+    const int rh = win_h / 2, rw = win_w / 2;
+    const int i = blockIdx.y, j0 = blockIdx.x * SAD_TJ;
+    const int ncol = SAD_TJ + 2 * rw;
+    for (int t = threadIdx.x; t < ncol * d; t += blockDim.x) {
+        const int cx = t / d, k = t % d;
+        const int xl = min(max(j0 + cx - rw, 0), w - 1);  // clamped window column (src/cost.cpp:45-46)
+        const int xr = max(xl - k / scale, 0);            // :47
+        unsigned acc = 0;
+        for (int a = -rh; a <= rh; ++a) {
+            const int y = min(max(i + a, 0), h - 1);
+            const int df = (int)__ldg(img_l + (size_t)y * w + xl) - (int)__ldg(img_r + (size_t)y * w + xr);
+            acc += (unsigned)(df * df);
+        }
+        vs32[t] = acc;
+    }
+    __syncthreads();
+    float* out = cost + (size_t)i * w * d;
+    for (int t = threadIdx.x; t < SAD_TJ * d; t += blockDim.x) {
+        const int cj = t / d, k = t % d;
+        const int j = j0 + cj;
+        if (j >= w) continue;
+        unsigned acc = 0;
+        for (int b = 0; b <= 2 * rw; ++b) acc += vs32[(cj + b) * d + k];
+        out[(size_t)j * d + k] = __fdiv_rn(__fdiv_rn((float)acc, (float)win_h), (float)win_w);
+    }
+}
+
+// src/cost.cpp:62-96 (CT) for every (pixel, d): a census string of the left window around (x, y) against one of the right
+// window, recomputed per disparity, with the function's own conventions: the right centre pixel is R(y, max(x - d, 0)) —
+// d NOT divided by scale (:69) — while the taps use x_r = x_l - d / scale and are DROPPED from both strings when x_r < 0
+// (:85-88); the strings are packed (v | bit) << 1, which the Hamming distance does not see.  So the cost is the number of
+// kept taps whose two comparisons disagree.  One block = (row, 32 columns); the 2*rh+1 rows of both images that the
+// windows touch are staged in shared memory, the right one D-1+rw columns further to the left.
+constexpr int CT_VOL_TJ = 32;
+__global__ void __launch_bounds__(256) ct_volume_kernel(const uint8_t* __restrict__ img_l, const uint8_t* __restrict__ img_r,
+                                                        float* __restrict__ cost, int h, int w, int d, int win_h, int win_w, int scale) {
+    extern __shared__ unsigned char ctsm[];
+    const int rh = win_h / 2, rw = win_w / 2, nrow = 2 * rh + 1;
+    const int i = blockIdx.y, j0 = blockIdx.x * CT_VOL_TJ;
+    const int lw = CT_VOL_TJ + 2 * rw;              // left tile: columns j0-rw .. j0+31+rw (clamped on load)
+    const int rshift = rw + d - 1;                  // right tile starts at column j0 - rshift
+    const int rwid = CT_VOL_TJ + rw + rshift;       // .. up to j0+31+rw
+    unsigned char* tl = ctsm;                       // [nrow][lw]
+    unsigned char* tr = ctsm + (size_t)nrow * lw;   // [nrow][rwid]
+    for (int t = threadIdx.x; t < nrow * lw; t += blockDim.x) {
+        const int r = t / lw, c = t % lw;
+        const int y = min(max(i + r - rh, 0), h - 1), x = min(max(j0 + c - rw, 0), w - 1);
+        tl[t] = __ldg(img_l + (size_t)y * w + x);
+    }
+    for (int t = threadIdx.x; t < nrow * rwid; t += blockDim.x) {
+        const int r = t / rwid, c = t % rwid;
+        const int y = min(max(i + r - rh, 0), h - 1), x = min(max(j0 + c - rshift, 0), w - 1);  // x < 0 is never used (dropped taps)
+        tr[t] = __ldg(img_r + (size_t)y * w + x);
+    }
+    __syncthreads();
+    float* out = cost + (size_t)i * w * d;
+    for (int t = threadIdx.x; t < CT_VOL_TJ * d; t += blockDim.x) {
+        const int cj = t / d, k = t % d;
+        const int x = j0 + cj;
+        if (x >= w) continue;
+        const int ks = k / scale;
+        const unsigned char cl = tl[rh * lw + cj + rw];                              // L(y, x)
+        const unsigned char cr = tr[rh * rwid + (max(x - k, 0) - (j0 - rshift))];    // R(y, max(x - d, 0))
+        int acc = 0;
+        for (int a = 0; a < nrow; ++a) {
+            for (int b = -rw; b <= rw; ++b) {
+                if (a == rh && b == 0) continue;
+                const int xl = min(max(x + b, 0), w - 1);
+                const int xr = xl - ks;
+                if (xr < 0) continue;
+                const bool bl = tl[a * lw + (xl - (j0 - rw))] > cl;
+                const bool br = tr[a * rwid + (xr - (j0 - rshift))] > cr;
+                acc += bl != br ? 1 : 0;
+            }
+        }
+        out[(size_t)x * d + k] = (float)acc;
+    }
+}
+
 // Banded form: a block owns SADB_XC window columns (SADB_XC - 2*rw output columns) x all D disparities and walks down a
 // band of rows.  Thread (k, g) keeps the vertical sums V(x, k) = sum_a |own(y+a, x) - other(y+a, x -/+ k)| of its
 // columns in registers and slides them one row at a time (+ the entering row, - the leaving row; the image rows of the
@@ -451,7 +537,10 @@ void launch_census(const uint8_t* img, uint64_t* table, int h, int w, int win_h,
 template <int WIN>
 static void launch_hh(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r, float* cost, int views,
                       int h, int w, int d, int scale, cudaStream_t st) {
-    static const bool legacy = std::getenv("SGM_B200_HFILTER_LEGACY") != nullptr;
+    bool legacy = false;  // the thread-per-(row, d) form below is the path of very wide rows; tuning builds can force it
+#ifdef SGM_B200_TUNING
+    legacy = std::getenv("SGM_B200_HFILTER_LEGACY") != nullptr;
+#endif
     const bool sky = sky_l || sky_r;
     const size_t smem = (size_t)(2 * w + d) * sizeof(uint64_t) + (sky ? (size_t)w : 0);
     if (legacy || smem > 200 * 1024) {  // very wide rows: the thread-per-(row, d) form that reads the tables through L1
@@ -581,7 +670,10 @@ static void launch_sad_band(const uint8_t* img_l, const uint8_t* img_r, const fl
 // lut (optional, device): lut[s] = (float(s) / win_h) / win_w for s = 0 .. 255 * win_h * win_w
 void launch_sad_volume(const uint8_t* img_l, const uint8_t* img_r, const float* lut, float* cost, int views, int h, int w, int d,
                        int win_h, int win_w, int scale, cudaStream_t st, LaunchCounter& lc) {
-    static const bool legacy = std::getenv("SGM_B200_SAD_LEGACY") != nullptr;
+    bool legacy = false;  // the per-row form below serves disparity counts / windows the banded kernel is not built for
+#ifdef SGM_B200_TUNING
+    legacy = std::getenv("SGM_B200_SAD_LEGACY") != nullptr;
+#endif
     const int rw = win_w / 2;
     const bool band_ok = !legacy && rw <= 12 && win_h <= 63 && (d == 8 || d == 16 || d == 32 || d == 64 || d == 128 || d == 256);
     if (band_ok) {
@@ -604,6 +696,36 @@ void launch_sad_volume(const uint8_t* img_l, const uint8_t* img_r, const float* 
     dim3 grid((w + SAD_TJ - 1) / SAD_TJ, h, views);
     sad_volume_kernel<<<grid, 256, smem, st>>>(img_l, img_r, cost, h, w, d, win_h, win_w, scale);
     lc.note("sad_volume_kernel");
+}
+
+// src/cost.cpp:33-59 / :62-96 as dense volumes of the left view, [h][w][d] floats, as Solver::build_dsi (src/Solver.cpp:96-117)
+// would fill them.  kind: 1 = SSD, 2 = CT.
+void launch_window_cost_volume(int kind, const uint8_t* img_l, const uint8_t* img_r, float* cost, int h, int w, int d, int win_h, int win_w,
+                               int scale, cudaStream_t st, LaunchCounter& lc) {
+    const int rh = win_h / 2, rw = win_w / 2;
+    if (kind == 1) {
+        const size_t smem = (size_t)(SAD_TJ + 2 * rw) * d * sizeof(unsigned);
+        if (smem > 200 * 1024 || (long long)win_h * win_w * 65025ll >= (1ll << 24)) {
+            lc.err = cudaErrorInvalidValue;
+            lc.failed = "ssd_volume_kernel (window too large for exact accumulation / shared memory)";
+            return;
+        }
+        if (smem > 48 * 1024) cudaFuncSetAttribute(ssd_volume_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        ssd_volume_kernel<<<dim3((w + SAD_TJ - 1) / SAD_TJ, h), 256, smem, st>>>(img_l, img_r, cost, h, w, d, win_h, win_w, scale);
+        lc.note("ssd_volume_kernel");
+    } else if (kind == 2) {
+        const size_t smem = (size_t)(2 * rh + 1) * ((CT_VOL_TJ + 2 * rw) + (CT_VOL_TJ + 2 * rw + d - 1));
+        if (smem > 200 * 1024 || (2 * rh + 1) * (2 * rw + 1) - 1 > 63) {  // the reference's 64-bit strings hold 63 taps
+            lc.err = cudaErrorInvalidValue;
+            lc.failed = "ct_volume_kernel (window too large)";
+            return;
+        }
+        if (smem > 48 * 1024) cudaFuncSetAttribute(ct_volume_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        ct_volume_kernel<<<dim3((w + CT_VOL_TJ - 1) / CT_VOL_TJ, h), 256, smem, st>>>(img_l, img_r, cost, h, w, d, win_h, win_w, scale);
+        lc.note("ct_volume_kernel");
+    } else {
+        lc.err = cudaErrorInvalidValue;
+    }
 }
 
 }  // namespace sgmb200

@@ -326,13 +326,9 @@ int run_frame(sgm_engine* e, const uint8_t* left, size_t lstride, const uint8_t*
 
     // ---- post stage ----
     if (e->timing) cudaEventRecord(e->ev[SGM_STAGE_POST], st);
-    if (e->views == 2) {
-        launch_lr_check(e->d_sub, e->d_sub + e->n, e->d_lr, e->d_med, h, w, D, s, p.lr_thresh, st, lc);  // src/SGM.cpp:803-818
-    } else {
-        cudaMemcpyAsync(e->d_lr, e->d_sub, e->n * sizeof(float), cudaMemcpyDeviceToDevice, st);
-        cudaMemcpyAsync(e->d_med, e->d_sub, e->n * sizeof(float), cudaMemcpyDeviceToDevice, st);
-    }
-    launch_median_fill(e->d_lr, e->d_med, h, w, D, p.median_h, p.median_w, st, lc);  // src/Solver.cpp:604-630
+    // src/SGM.cpp:803-818 (LR check; BM has one view and none) + src/Solver.cpp:604-630 (hole-filling median)
+    launch_lr_median(e->d_sub, e->views == 2 ? e->d_sub + e->n : nullptr, e->d_lr, e->d_med, e->d_label, e->d_area, h, w, D, s, p.lr_thresh,
+                     p.median_h, p.median_w, st, lc);
     launch_speckle(e->d_med, e->d_final, e->d_label, e->d_area, h, w, (float)(D + 1), p.speckle_size / s, (float)p.speckle_dis, st,
                    lc);                                                              // src/Solver.cpp:634
     if (e->timing) cudaEventRecord(e->ev[SGM_STAGE_DOWNLOAD], st);
@@ -751,6 +747,44 @@ int sgm_cost_volume_sad(int device, const uint8_t* left, const uint8_t* right, i
     cudaFree(d_lut);
     if (c != cudaSuccess) return fail(nullptr, SGM_ERR_CUDA, "sgm_cost_volume_sad: %s", cudaGetErrorString(c));
     return SGM_OK;
+}
+
+namespace {
+int window_cost_volume(int kind, const char* name, int device, const uint8_t* left, const uint8_t* right, int height, int width, int max_disp,
+                       int win_h, int win_w, int scale, float* out) {
+    if (!left || !right || !out || height <= 0 || width <= 0 || max_disp <= 0 || scale <= 0 || win_h <= 0 || win_w <= 0)
+        return fail(nullptr, SGM_ERR_INVALID, "%s: bad argument", name);
+    if (cudaSetDevice(device) != cudaSuccess) return fail(nullptr, SGM_ERR_CUDA, "no CUDA device %d: this engine has no CPU path", device);
+    const size_t n = (size_t)height * width, N = n * max_disp;
+    uint8_t* d_img = nullptr;
+    float* d_cost = nullptr;
+    cudaError_t c = cudaMalloc(reinterpret_cast<void**>(&d_img), 2 * n);
+    if (c == cudaSuccess) c = cudaMalloc(reinterpret_cast<void**>(&d_cost), N * sizeof(float));
+    if (c == cudaSuccess) c = cudaMemcpy(d_img, left, n, cudaMemcpyHostToDevice);
+    if (c == cudaSuccess) c = cudaMemcpy(d_img + n, right, n, cudaMemcpyHostToDevice);
+    LaunchCounter lc;
+    if (c == cudaSuccess) {
+        launch_window_cost_volume(kind, d_img, d_img + n, d_cost, height, width, max_disp, win_h, win_w, scale, nullptr, lc);
+        c = lc.err;
+    }
+    const bool rejected = c == cudaErrorInvalidValue && lc.failed;
+    if (c == cudaSuccess) c = cudaMemcpy(out, d_cost, N * sizeof(float), cudaMemcpyDeviceToHost);
+    cudaFree(d_img);
+    cudaFree(d_cost);
+    if (rejected) return fail(nullptr, SGM_ERR_UNSUPPORTED, "%s: %s", name, lc.failed);
+    if (c != cudaSuccess) return fail(nullptr, SGM_ERR_CUDA, "%s: %s", name, cudaGetErrorString(c));
+    return SGM_OK;
+}
+}  // namespace
+
+int sgm_cost_volume_ssd(int device, const uint8_t* left, const uint8_t* right, int height, int width, int max_disp, int win_h, int win_w,
+                        int scale, float* out) {
+    return window_cost_volume(1, "sgm_cost_volume_ssd", device, left, right, height, width, max_disp, win_h, win_w, scale, out);
+}
+
+int sgm_cost_volume_ct(int device, const uint8_t* left, const uint8_t* right, int height, int width, int max_disp, int win_h, int win_w,
+                       int scale, float* out) {
+    return window_cost_volume(2, "sgm_cost_volume_ct", device, left, right, height, width, max_disp, win_h, win_w, scale, out);
 }
 
 }  // extern "C"

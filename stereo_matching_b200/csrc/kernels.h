@@ -51,6 +51,10 @@ void launch_vfilter(float* cost, int views, int h, int w, int d, int win, cudaSt
 void launch_sad_volume(const uint8_t* img_l, const uint8_t* img_r, const float* lut, float* cost, int views, int h, int w, int d,
                        int win_h, int win_w, int scale, cudaStream_t st, LaunchCounter& lc);
 
+// src/cost.cpp:33-59 (SSD, kind 1) / :62-96 (CT, kind 2) for every (pixel, d) of the left view.
+void launch_window_cost_volume(int kind, const uint8_t* img_l, const uint8_t* img_r, float* cost, int h, int w, int d, int win_h, int win_w,
+                               int scale, cudaStream_t st, LaunchCounter& lc);
+
 // ---- aggregation (aggregate_kernels.cu) ------------------------------------------------------
 struct AggregateArgs {
     const float* cost;  // [views][n*d]   filtered cost volume C
@@ -80,14 +84,11 @@ void launch_wta(const float* vol, uint16_t* disp, float* subpixel, int views, in
                 int min_gap, int parabola, cudaStream_t st, LaunchCounter& lc);
 
 // ---- post stage (post_kernels.cu) --------------------------------------------------------------
-// src/SGM.cpp:803-818.
-// The checked image is written to both out_keep (tap) and out_work (the buffer the median then updates in place).
-void launch_lr_check(const float* left, const float* right, float* out_keep, float* out_work, int h, int w, int d,
-                     int scale, float thresh, cudaStream_t st, LaunchCounter& lc);
-// src/Solver.cpp:604-630, exact raster-order semantics through a wavefront.  `src` = read-only copy of the
-// image before filling, `f` = the image being filled in place (same content on entry).
-void launch_median_fill(const float* src, float* f, int h, int w, int d, int win_h, int win_w, cudaStream_t st,
-                        LaunchCounter& lc);
+// src/SGM.cpp:803-818 (LR check of the left sub-pixel image against the right one; right == nullptr: none, BM) fused with the
+// hole-filling median of src/Solver.cpp:604-630 (exact raster-order semantics).  out_lr = the checked image (tap), out_med =
+// the checked image with the holes filled.  scratch_a / scratch_b: int buffers of h * w elements each (contents destroyed).
+void launch_lr_median(const float* left, const float* right, float* out_lr, float* out_med, int* scratch_a, int* scratch_b, int h, int w,
+                      int d, int scale, float thresh, int win_h, int win_w, cudaStream_t st, LaunchCounter& lc);
 // src/Solver.cpp:514-566 with serial semantics: f_out = f_in with small components set to `value`;
 // labels / area are n-int scratch buffers.
 void launch_speckle(const float* f_in, float* f_out, int* labels, int* area, int h, int w, float value, int max_size,

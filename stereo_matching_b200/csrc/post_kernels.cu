@@ -18,309 +18,280 @@ namespace {
 // address (cudaGetSymbolAddress, once per device) and the launcher passes that pointer to the kernels.
 static __device__ __align__(256) int g_speckle_static_scratch[2 * (size_t)SPECKLE_STATIC_MAX_PIXELS];
 
-// src/SGM.cpp:803-818: for j >= dl: dr = right(i, int(j - dl/scale)); |dl - dr| > thresh -> dl = D+1.
-// Writes the result twice: `out_keep` (the LR tap) and `out_work` (the buffer the median updates in place).
-__global__ void lr_check_kernel(const float* __restrict__ left, const float* __restrict__ right, float* __restrict__ out_keep,
-                                float* __restrict__ out_work, int h, int w, int d, int scale, float thresh) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    const int i = blockIdx.y;
-    if (j >= w) return;
-    const size_t p = (size_t)i * w + j;
-    float dl = left[p];
-    if ((float)j >= dl) {
-        const int jr = (int)__fsub_rn((float)j, __fdiv_rn(dl, (float)scale));
-        // 0 <= jr <= j holds for every finite dl >= 0; the guard only keeps a non-finite dl (which the reference
-        // would index out of bounds with) from faulting
-        if (jr >= 0 && jr < w) {
-            const float dr = right[(size_t)i * w + jr];
-            if (fabsf(__fsub_rn(dl, dr)) > thresh) dl = (float)(d + 1);
-        }
+// ---------------------------------------------------------------------------------------------
+// LR check (src/SGM.cpp:803-818) fused with the first half of the hole-filling median (src/Solver.cpp:604-630).
+//
+// The reference fills holes IN PLACE in raster order: an interior pixel whose value is invalid (> D-1) takes
+// sorted[cnt / 2] of the valid values of its WH x WW window (truncated to int) when more than half of the window is valid,
+// and later pixels see that fill.  Only a hole can change, and only another hole earlier in raster order inside its
+// window ("causal" cells: the rows above and the cells to the left) can change what it sees.  So:
+//   * a hole whose valid neighbours plus causal holes cannot exceed half the window can NEVER be filled, whatever happens
+//     before it; it needs no ordering at all.  On real frames that leaves a few hundred CANDIDATES out of ~10^4 holes
+//     (the interior of occlusion bands and of the invalid left margin drops out at once);
+//   * the candidates form a shallow dependency DAG (depth 20 - 70 on SGM frames, a few hundred on block matching).
+// lr_classify_kernel does the LR check for a tile plus halo in shared memory, writes the checked image (twice: the LR tap
+// and the image the median updates) and one bit per pixel: "candidate".  median_solve_kernel (one block) then compacts
+// the bits in raster order and resolves the candidates in shared memory.  Replaces a 2700-step wavefront over every pixel.
+template <int WH, int WW>
+struct MedianWin {
+    static constexpr int RH = WH / 2, RW = WW / 2, NWIN = WH * WW, NB = NWIN - 1, NC = RH * WW + RW;  // neighbours; causal ones first
+    __device__ static __forceinline__ void offset(int t, int& a, int& b) {  // t-th neighbour in row-major order, centre skipped
+        const int u = t < NC ? t : t + 1;
+        a = u / WW - RH;
+        b = u % WW - RW;
     }
-    out_keep[p] = dl;
-    out_work[p] = dl;
+};
+
+constexpr int LRC_TX = 32, LRC_TY = 8;
+
+template <int WH, int WW>
+__global__ void __launch_bounds__(LRC_TX* LRC_TY) lr_classify_kernel(const float* __restrict__ left, const float* __restrict__ right,
+                                                                     float* __restrict__ out_keep, float* __restrict__ out_work,
+                                                                     unsigned* __restrict__ bitmap, int h, int w, int d, int scale,
+                                                                     float thresh) {
+    using MW = MedianWin<WH, WW>;
+    constexpr int RH = MW::RH, RW = MW::RW, TH = LRC_TY + 2 * RH, TW = LRC_TX + 2 * RW;
+    __shared__ float tile[TH][TW + 1];
+    const int i0 = blockIdx.y * LRC_TY, j0 = blockIdx.x * LRC_TX;
+    const float vmax = (float)(d - 1);
+    for (int t = threadIdx.y * LRC_TX + threadIdx.x; t < TH * TW; t += LRC_TX * LRC_TY) {
+        const int ti = t / TW, tj = t % TW, i = i0 - RH + ti, j = j0 - RW + tj;
+        float dl = INFINITY;  // outside the image: never read by an interior pixel's window
+        if (i >= 0 && i < h && j >= 0 && j < w) {
+            const size_t p = (size_t)i * w + j;
+            dl = left[p];
+            if (right && (float)j >= dl) {  // src/SGM.cpp:803-818: for j >= dl: dr = right(i, int(j - dl/scale)); |dl - dr| > thresh -> D+1
+                const int jr = (int)__fsub_rn((float)j, __fdiv_rn(dl, (float)scale));
+                // 0 <= jr <= j holds for every finite dl >= 0; the guard only keeps a non-finite dl (which the reference
+                // would index out of bounds with) from faulting
+                if (jr >= 0 && jr < w) {
+                    const float dr = right[(size_t)i * w + jr];
+                    if (fabsf(__fsub_rn(dl, dr)) > thresh) dl = (float)(d + 1);
+                }
+            }
+            if (ti >= RH && ti < RH + LRC_TY && tj >= RW && tj < RW + LRC_TX) {
+                out_keep[p] = dl;
+                out_work[p] = dl;
+            }
+        }
+        tile[ti][tj] = dl;
+    }
+    __syncthreads();
+    const int i = i0 + threadIdx.y, j = j0 + threadIdx.x;
+    auto interior = [&](int y, int x) { return y >= RH && y < h - RH && x >= RW && x < w - RW; };
+    bool cand = false;
+    if (i < h && j < w && interior(i, j) && !(tile[threadIdx.y + RH][threadIdx.x + RW] <= vmax)) {
+        int reach = 0;  // valid neighbours + causal holes that might still be filled
+#pragma unroll
+        for (int t = 0; t < MW::NB; ++t) {
+            int a, b;
+            MW::offset(t, a, b);
+            const bool ok = tile[threadIdx.y + RH + a][threadIdx.x + RW + b] <= vmax;
+            reach += (ok || (t < MW::NC && interior(i + a, j + b))) ? 1 : 0;
+        }
+        cand = reach > MW::NWIN / 2;
+    }
+    const unsigned word = __ballot_sync(FULL_MASK, cand);  // one warp = one tile row = one bitmap word
+    if (threadIdx.x == 0 && i < h) bitmap[(size_t)i * gridDim.x + blockIdx.x] = word;
 }
 
-// src/Solver.cpp:604-630.  The reference fills holes IN PLACE in raster order, so a pixel sees the fills of
-// earlier pixels in its window.  Pixel (i, j) depends on rows i-rh..i-1 up to column j+rw and on row i left
-// of j; the wavefront t = j + (rw+1)*i orders all of those strictly before it.  One block walks the
-// wavefront, one row per thread (rows strided over the block when h > blockDim).  `src` is the read-only
-// pre-filter image (a pixel is only ever written by its own step, so src tells whether it is a hole without
-// touching the buffer being updated); holes gather their window from `f` through L2 (__ldcg).
-template <int WH, int WW>
-__global__ void __launch_bounds__(1024) median_fill_kernel(const float* __restrict__ src, float* f, int h, int w, int d) {
-    constexpr int RH = WH / 2, RW = WW / 2, K = RW + 1, NWIN = WH * WW;
+// Second half: ONE block resolves the candidates.
+//   1. ordered compaction of the candidate bits: per-row counts (warp per row, lane per bitmap word), block scan over the
+//      rows, then every set bit gets its raster-order index; `wordoff` keeps the index of the first candidate of every
+//      bitmap word, so "which candidate is pixel q" is one look-up plus a popcount;
+//   2. in chunks of CHUNK candidates (raster order): every candidate's window goes to shared memory as 16-bit entries —
+//      a literal value (already final: a non-hole, a hole that can never be filled, or a fill of an earlier chunk) or a
+//      REFERENCE to an earlier candidate of the same chunk;
+//   3. rounds: a candidate whose references are all resolved takes its median (or stays invalid); one that can no longer
+//      reach half a window of valid values is dropped early.  The first unresolved candidate in raster order has no
+//      unresolved reference, so every round resolves something; the number of rounds is the depth of the dependency DAG.
+// Window entries: 0 .. 0x7ffe literal (int)value (the reference truncates to int, src/Solver.cpp:619), 0x7fff invalid,
+// 0x8000 | k reference to candidate k of the chunk.  val[k]: 0xffff unresolved, else like a literal.
+constexpr unsigned short MED_INVALID = 0x7fff, MED_UNRESOLVED = 0xffff;
+
+template <int WH, int WW, int CHUNK>
+__global__ void __launch_bounds__(1024) median_solve_kernel(float* f, const unsigned* __restrict__ bitmap, int* wordoff, int* rowoff, int* list,
+                                                            int h, int w, int d) {
+    using MW = MedianWin<WH, WW>;
+    constexpr int NB = MW::NB, NC = MW::NC, HALF = MW::NWIN / 2;
+    extern __shared__ __align__(16) unsigned char msm[];
+    unsigned short* win = reinterpret_cast<unsigned short*>(msm);            // [CHUNK][NB]
+    unsigned short* val = win + (size_t)CHUNK * NB;                            // [CHUNK]
+    unsigned char* litv = reinterpret_cast<unsigned char*>(val + CHUNK);       // [CHUNK] literal valid entries of the window
+    __shared__ int wsum[32];
+    __shared__ int total_s;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nwarp = blockDim.x >> 5;
+    const int nw = (w + 31) / 32;
     const float vmax = (float)(d - 1);
-    const int steps = (w - 1) + K * (h - 1) + 1;
-    for (int t = 0; t < steps; ++t) {
-        for (int i = threadIdx.x; i < h; i += blockDim.x) {
-            const int j = t - K * i;
-            if (j < RW || j >= w - RW || i < RH || i >= h - RH) continue;
-            if (__ldg(src + (size_t)i * w + j) <= vmax) continue;  // not a hole
-            int vals[NWIN];
-            int cnt = 0;
+
+    // ---- 1a. per-row counts and row-relative word offsets ----
+    for (int i = wid; i < h; i += nwarp) {
+        int total = 0;
+        for (int jw0 = 0; jw0 < nw; jw0 += 32) {
+            const int jw = jw0 + lane;
+            const int c = jw < nw ? __popc(bitmap[(size_t)i * nw + jw]) : 0;
+            int inc = c;
 #pragma unroll
-            for (int a = -RH; a <= RH; ++a)
-#pragma unroll
-                for (int b = -RW; b <= RW; ++b) {
-                    const float v = __ldcg(f + (size_t)(i + a) * w + (j + b));
-                    const bool ok = v <= vmax;
-                    vals[(a + RH) * WW + (b + RW)] = ok ? (int)v : 0x7fffffff;  // float -> int truncation (:619)
-                    cnt += ok ? 1 : 0;
-                }
-            if (cnt > NWIN / 2) {
-                // sorted[cnt / 2] by rank counting (ties broken by position): invalid entries sort last
-                const int want = cnt / 2;
-                int pick = 0;
-#pragma unroll
-                for (int x = 0; x < NWIN; ++x) {
-                    int rank = 0;
-#pragma unroll
-                    for (int y = 0; y < NWIN; ++y) rank += (vals[y] < vals[x] || (vals[y] == vals[x] && y < x)) ? 1 : 0;
-                    if (rank == want) pick = vals[x];
-                }
-                f[(size_t)i * w + j] = (float)pick;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int x = __shfl_up_sync(FULL_MASK, inc, o);
+                if (lane >= o) inc += x;
             }
+            if (jw < nw) wordoff[(size_t)i * nw + jw] = total + inc - c;
+            total += __shfl_sync(FULL_MASK, inc, 31);
+        }
+        if (lane == 0) rowoff[i] = total;
+    }
+    __syncthreads();
+    // ---- 1b. exclusive scan of the row counts (contiguous rows per thread, then the classic two-level scan) ----
+    {
+        const int per = (h + (int)blockDim.x - 1) / (int)blockDim.x, r0 = tid * per, r1 = min(h, r0 + per);
+        int mine = 0;
+        for (int r = r0; r < r1; ++r) mine += rowoff[r];
+        int inc = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int x = __shfl_up_sync(FULL_MASK, inc, o);
+            if (lane >= o) inc += x;
+        }
+        if (lane == 31) wsum[wid] = inc;
+        __syncthreads();
+        if (wid == 0) {
+            const int v = lane < nwarp ? wsum[lane] : 0;
+            int winc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int x = __shfl_up_sync(FULL_MASK, winc, o);
+                if (lane >= o) winc += x;
+            }
+            wsum[lane] = winc - v;
+            if (lane == 31) total_s = winc;
         }
         __syncthreads();
+        int run = wsum[wid] + inc - mine;
+        for (int r = r0; r < r1; ++r) {
+            const int c = rowoff[r];
+            rowoff[r] = run;
+            run += c;
+        }
     }
-}
-
-// Fast form of the same wavefront.  Every row keeps a 32-column ring in shared memory that holds the CURRENT
-// value of its pixels around the wavefront (final values behind the row's cursor, original values ahead of it);
-// with the skew K = RW+1 the window of any hole lies within +-(K*RH + RW) <= 8 columns of each neighbouring row's
-// cursor, so holes gather their 25 values from shared memory instead of L2.  Original values stream into the ring
-// with cp.async (LDGSTS, global -> shared without registers) issued LEAD steps before they are needed, one commit
-// group per step, so a step costs one barrier and a handful of instructions; the median of a filled hole is found
-// by bisection on the value (ints in [0, D-1]).
-template <int WH, int WW, int RPT>
-__global__ void __launch_bounds__(1024) median_fill_ring_kernel(const float* __restrict__ src, float* __restrict__ f, int h, int w,
-                                                                int d) {
-    constexpr int RH = WH / 2, RW = WW / 2, K = RW + 1, NWIN = WH * WW, RING = 32, AHEAD = K * RH + RW + 1, LEAD = 8;
-    static_assert(K * RH + RW <= 8 && AHEAD + LEAD + K * RH + RW < RING, "window does not fit the ring");
-    extern __shared__ float ring[];  // [h][RING]
-    const float vmax = (float)(d - 1);
-    const int T = blockDim.x;
-    // Row i's cursor at step t is column c = t - K*i.  At step t it requests the original of column c + AHEAD + LEAD;
-    // the request of step t-LEAD (column c + AHEAD) has landed before this step's barrier.
-    const int t_end = (w - 1) + K * (h - 1);
-    for (int t = -(AHEAD + LEAD); t <= t_end; ++t) {
-#pragma unroll
-        for (int rr = 0; rr < RPT; ++rr) {
-            const int i = threadIdx.x + rr * T;
-            if (i < h) {
-                const int cf = t - K * i + AHEAD + LEAD;
-                if (cf >= 0 && cf < w) {
-                    const unsigned dst = (unsigned)__cvta_generic_to_shared(ring + (size_t)i * RING + (cf & (RING - 1)));
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src + (size_t)i * w + cf));
-                }
+    __syncthreads();
+    const int ncand = total_s;
+    if (ncand == 0) return;
+    // ---- 1c. absolute word offsets and the candidate list ----
+    for (int i = wid; i < h; i += nwarp) {
+        const int base = rowoff[i];
+        for (int jw = lane; jw < nw; jw += 32) {
+            const size_t wi = (size_t)i * nw + jw;
+            int k = wordoff[wi] + base;
+            wordoff[wi] = k;
+            unsigned word = bitmap[wi];
+            while (word) {
+                const int bit = __ffs(word) - 1;
+                word &= word - 1;
+                list[k++] = i * w + jw * 32 + bit;
             }
         }
-        asm volatile("cp.async.commit_group;");
-        asm volatile("cp.async.wait_group %0;" ::"n"(LEAD - 1));
-            __syncthreads();  // ring contents of this step's feeds and of the previous step's fills are visible
+    }
+    __syncthreads();
+
+    // ---- 2 / 3. chunks of candidates ----
+    for (int base = 0; base < ncand; base += CHUNK) {
+        const int cn = min(CHUNK, ncand - base);
+        for (int c = tid; c < cn; c += blockDim.x) {
+            const int p = list[base + c], i = p / w, j = p - i * w;
+            int nlit = 0;
 #pragma unroll
-            for (int rr = 0; rr < RPT; ++rr) {
-                const int i = threadIdx.x + rr * T;
-                if (i >= RH && i < h - RH) {
-                    const int c = t - K * i;
-                    if (c >= RW && c < w - RW) {
-                        const float own = ring[(size_t)i * RING + (c & (RING - 1))];
-                        if (!(own <= vmax)) {  // a hole
-                            int vals[NWIN];
-                            int cnt = 0;
-#pragma unroll
-                            for (int a = -RH; a <= RH; ++a)
-#pragma unroll
-                                for (int b = -RW; b <= RW; ++b) {
-                                    const float v = ring[(size_t)(i + a) * RING + ((c + b) & (RING - 1))];
-                                    const bool ok = v <= vmax;
-                                    vals[(a + RH) * WW + (b + RW)] = ok ? (int)v : 0x7fffffff;  // float -> int truncation (:619)
-                                    cnt += ok ? 1 : 0;
-                                }
-                            if (cnt > NWIN / 2) {
-                                // sorted[cnt / 2] = smallest v with #(vals <= v) >= cnt/2 + 1; bisection over [0, D-1]
-                                const int need = cnt / 2 + 1;
-                                int lo = 0, hi = d - 1;
-                                while (lo < hi) {
-                                    const int mid = (lo + hi) >> 1;
-                                    int le = 0;
-#pragma unroll
-                                    for (int x = 0; x < NWIN; ++x) le += vals[x] <= mid ? 1 : 0;
-                                    if (le >= need)
-                                        hi = mid;
-                                    else
-                                        lo = mid + 1;
-                                }
-                                const float fill = (float)lo;
-                                f[(size_t)i * w + c] = fill;
-                                // publish for later pixels: nobody reads this ring slot before the next barrier
-                                ring[(size_t)i * RING + (c & (RING - 1))] = fill;
-                            }
+            for (int t = 0; t < NB; ++t) {
+                int a, b;
+                MW::offset(t, a, b);
+                const int y = i + a, x = j + b;
+                unsigned short e = 0;
+                bool is_ref = false;
+                if (t < NC) {  // a causal cell may be an earlier candidate of this chunk
+                    const size_t wi = (size_t)y * nw + (x >> 5);
+                    const unsigned word = bitmap[wi];
+                    if ((word >> (x & 31)) & 1u) {
+                        const int k = wordoff[wi] + __popc(word & ((1u << (x & 31)) - 1u));
+                        if (k >= base) {
+                            e = (unsigned short)(0x8000u | (unsigned)(k - base));
+                            is_ref = true;
                         }
                     }
                 }
-            }
-        // the fills written above are ordered before the next step's gathers by the next step's barrier
-    }
-}
-
-// Batched form of the ring wavefront.  With a skew of K columns per row, a row may advance B = K - RW consecutive columns
-// between two barriers: a hole at (i, c + b), b < B, needs row i-1 final up to column c + b + RW <= c + K - 1, which row
-// i-1 (cursor c + K) finished in earlier batches, and rows below have not touched what it reads (their cursors trail by
-// K, 2K, ...).  Same raster-order result with (W + K*H) / B barriers instead of W + 3*H.
-template <int WH, int WW, int K, int RING, int LEADB, int COOP_MAX>
-__global__ void __launch_bounds__(1024) median_fill_batch_kernel(const float* __restrict__ src, float* __restrict__ f, int h, int w,
-                                                                  int d) {
-    constexpr int RH = WH / 2, RW = WW / 2, B = K - RW, NWIN = WH * WW, LOOK = K * RH + RW, AHEAD = LOOK + 1;
-    static_assert(B >= 1 && AHEAD + LEADB * B + B + LOOK < RING && (RING & (RING - 1)) == 0, "window does not fit the ring");
-    // rows are RS = RING + 1 floats apart: with one row per lane a power-of-two stride would put all 32 lanes of a warp on
-    // the same shared-memory bank (a 32-way conflict on every column check, feed and gather)
-    constexpr int RS = RING + 1;
-    extern __shared__ float ring[];  // [h][RS]
-    const float vmax = (float)(d - 1);
-    // Values that never change are pinned in registers through opaque moves: left alone, the compiler re-derives them in
-    // every batch (S2R tid, the shared window base, the row's limits), which lengthens the loop's dependent chain.
-    auto pin = [](unsigned v) {
-        unsigned r;
-        asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(v));
-        return r;
-    };
-    const int i = (int)pin(threadIdx.x);  // one row per thread (h <= blockDim.x)
-    const int lane = i & 31;
-    static_assert(NWIN <= 32, "the window must fit a warp");
-    // COOP_MAX: up to this many holes per warp and column are filled one after the other by the whole warp
-    const bool row_ok = i < h;
-    const bool interior_row = i >= RH && i < h - RH;
-    float* myring = ring + (size_t)(row_ok ? i : 0) * RS;
-    const float* mysrc = src + (size_t)(row_ok ? i : 0) * w;
-    const unsigned myring_s = pin((unsigned)__cvta_generic_to_shared(myring));  // shared-space address: offsets fold into the cp.async
-    // batch n: row i's cursor is c = n*B - K*i.  First batch: the top row needs its first AHEAD + LEADB*B columns requested.
-    const int n_first = -((AHEAD + LEADB * B + B - 1) / B);
-    const int n_last = ((w - 1) + K * (h - 1)) / B;
-    // The batch loop is a chain of dependent instructions executed ~W + K*H times, so everything that does not change is
-    // kept out of it: the cursor and the feed address advance by B, range tests are single unsigned compares.
-    int c = n_first * B - K * i;
-    long long feed = (long long)(size_t)mysrc + 4ll * (c + AHEAD + LEADB * B);  // address of column c + AHEAD + LEADB*B of this row
-    const unsigned feed_lim = pin(row_ok ? (unsigned)w : 0u);                  // columns [0, w) are fed
-    const unsigned hole_lim = pin(interior_row ? (unsigned)(w - 2 * RW) : 0u);  // columns [RW, w - RW) can be holes
-    for (int n = n_first; n <= n_last; ++n, c += B, feed += 4 * B) {
-        {
-            const int cf = c + AHEAD + LEADB * B;
-#pragma unroll
-            for (int b = 0; b < B; ++b) {
-                const int x = cf + b;
-                if ((unsigned)x < feed_lim) {
-                    const unsigned dst = myring_s + (unsigned)(x & (RING - 1)) * 4u;
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(feed + 4 * b));
+                if (!is_ref) {  // final already (earlier chunks wrote their fills back before this chunk was built)
+                    const float v = f[(size_t)y * w + x];
+                    const bool ok = v <= vmax;
+                    e = ok ? (unsigned short)(int)v : MED_INVALID;
+                    nlit += ok ? 1 : 0;
                 }
+                win[(size_t)c * NB + t] = e;
             }
+            litv[c] = (unsigned char)nlit;
+            val[c] = MED_UNRESOLVED;
         }
-        asm volatile("cp.async.commit_group;");
-        asm volatile("cp.async.wait_group %0;" ::"n"(LEADB));
-        __syncthreads();  // feeds of batch n - LEADB and the fills of batch n - 1 are visible
-        // Holes of this batch are filled warp-cooperatively: the warp votes which of its 32 rows have a hole at column
-        // c + b, then for each such hole 25 lanes gather one window element each and the median comes from a bisection
-        // on ballots (the values are integers in [0, D-1]).  Columns b = 0 .. B-1 go in order because a fill changes what
-        // the next column of the same row sees; different rows of a batch are independent (see above).
-        // Which pixels of the batch are holes is known up front (a fill only ever writes the hole it fills, and every
-        // position is examined once), so the B shared-memory reads and votes are issued together instead of one
-        // dependent read -> compare -> vote chain per column; columns without a hole in this warp then cost nothing.
-        unsigned votes[B];
+        __syncthreads();
+        volatile unsigned short* vval = val;
+        for (;;) {
+            int open = 0;
+            for (int c = tid; c < cn; c += blockDim.x) {
+                if (vval[c] != MED_UNRESOLVED) continue;
+                const unsigned short* wc = win + (size_t)c * NB;
+                int unknown = 0, refvalid = 0;
+                unsigned short rv[NC];
 #pragma unroll
-        for (int b = 0; b < B; ++b) {
-            const int x = c + b;
-            float v;  // any slot is readable; the range test decides whether it counts
-            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(myring_s + (unsigned)(x & (RING - 1)) * 4u));
-            votes[b] = __ballot_sync(FULL_MASK, (unsigned)(x - RW) < hole_lim && !(v <= vmax));
-        }
-#pragma unroll 1
-        for (int b = 0; b < B; ++b) {
-            unsigned todo = votes[0];
+                for (int t = 0; t < NC; ++t) {
+                    const unsigned short e = wc[t];
+                    unsigned short x = e;
+                    if (e & 0x8000u) {
+                        x = vval[e & 0x7fffu];
+                        unknown += x == MED_UNRESOLVED ? 1 : 0;
+                        refvalid += (x != MED_UNRESOLVED && x != MED_INVALID) ? 1 : 0;
+                    }
+                    rv[t] = x;
+                }
+                const int known = (int)litv[c] + refvalid;
+                if (unknown == 0) {
+                    unsigned short out = MED_INVALID;
+                    if (known > HALF) {
+                        // sorted[cnt / 2] = the smallest value with at least cnt / 2 + 1 window values <= it (bisection)
+                        int vals[NB];
+                        int lo = 0x7fff, hi = 0;
 #pragma unroll
-            for (int q = 1; q < B; ++q) todo = b == q ? votes[q] : todo;
-            if (todo == 0) continue;
-            const int x = c + b;
-            const bool hole = (todo >> lane) & 1u;
-            if (__popc(todo) > COOP_MAX) {
-                // many rows of this warp have a hole in this column (occlusion bands, the invalid left margin): every such
-                // lane fills its own hole, all of them in parallel, with the same bisection on its private window
-                if (hole) {
-                    int vals[NWIN];
-                    int cnt = 0, vlo = 0x7fffffff, vhi = 0;
-#pragma unroll
-                    for (int a = -RH; a <= RH; ++a)
-#pragma unroll
-                        for (int e = -RW; e <= RW; ++e) {
-                            const float v = ring[(size_t)(i + a) * RS + ((x + e) & (RING - 1))];
-                            const bool ok = v <= vmax;
-                            const int iv = ok ? (int)v : 0x7fffffff;  // float -> int truncation (:619)
-                            vals[(a + RH) * WW + (e + RW)] = iv;
-                            cnt += ok ? 1 : 0;
-                            vlo = min(vlo, iv);
-                            vhi = ok ? max(vhi, iv) : vhi;
+                        for (int t = 0; t < NB; ++t) {
+                            const int x = t < NC ? (int)rv[t] : (int)wc[t];
+                            vals[t] = x;  // invalid = 0x7fff sorts last
+                            if (x != MED_INVALID) {
+                                lo = min(lo, x);
+                                hi = max(hi, x);
+                            }
                         }
-                    if (cnt > NWIN / 2) {
-                        // the median lies between the smallest and the largest valid value: neighbouring disparities are
-                        // close, so the bisection usually needs one or two rounds instead of log2(D)
-                        const int need = cnt / 2 + 1;
-                        int lo = vlo, hi = vhi;
+                        const int need = known / 2 + 1;
                         while (lo < hi) {
                             const int mid = (lo + hi) >> 1;
                             int le = 0;
 #pragma unroll
-                            for (int q = 0; q < NWIN; ++q) le += vals[q] <= mid ? 1 : 0;
+                            for (int t = 0; t < NB; ++t) le += vals[t] <= mid ? 1 : 0;
                             if (le >= need)
                                 hi = mid;
                             else
                                 lo = mid + 1;
                         }
-                        const float fill = (float)lo;
-                        f[(size_t)i * w + x] = fill;
-                        myring[x & (RING - 1)] = fill;
+                        out = (unsigned short)lo;
                     }
+                    vval[c] = out;
+                } else if (known + unknown <= HALF) {
+                    vval[c] = MED_INVALID;  // can no longer reach half a window: resolved without waiting
+                } else {
+                    ++open;
                 }
-                __syncwarp();
-                todo = 0;
             }
-            while (todo) {
-                const int src = __ffs(todo) - 1;
-                todo &= todo - 1;
-                const int i0 = (int)(threadIdx.x & ~31u) + src;
-                const int x0 = __shfl_sync(FULL_MASK, x, src);
-                bool ok = false;
-                int val = 0x7fffffff;
-                if (lane < NWIN) {
-                    const int a = lane / WW - RH, e = lane % WW - RW;
-                    const float v = ring[(size_t)(i0 + a) * RS + ((x0 + e) & (RING - 1))];
-                    ok = v <= vmax;
-                    if (ok) val = (int)v;  // float -> int truncation (src/Solver.cpp:619)
-                }
-                const int cnt = __popc(__ballot_sync(FULL_MASK, ok));
-                if (cnt > NWIN / 2) {
-                    // sorted[cnt / 2] = the smallest value v with at least cnt / 2 + 1 window values <= v: a bisection on
-                    // ballots between the smallest and the largest valid value (two warp reductions).  Neighbouring
-                    // disparities are close, so it takes zero to three rounds; ranking every value against every other
-                    // (25 shuffles) took longer.
-                    int lo = __reduce_min_sync(FULL_MASK, val);
-                    int hi = __reduce_max_sync(FULL_MASK, ok ? val : -1);
-                    const int need = cnt / 2 + 1;
-                    while (lo < hi) {
-                        const int mid = (lo + hi) >> 1;
-                        const int le = __popc(__ballot_sync(FULL_MASK, val <= mid));  // invalid entries are INT_MAX
-                        if (le >= need)
-                            hi = mid;
-                        else
-                            lo = mid + 1;
-                    }
-                    if (lane == 0) {
-                        const float fill = (float)lo;
-                        f[(size_t)i0 * w + x0] = fill;
-                        ring[(size_t)i0 * RS + (x0 & (RING - 1))] = fill;  // later columns of this row, and everyone after the barrier
-                    }
-                }
-                __syncwarp();
-            }
+            if (__syncthreads_count(open) == 0) break;
         }
+        for (int c = tid; c < cn; c += blockDim.x) {
+            const unsigned short v = val[c];
+            if (v != MED_INVALID) f[list[base + c]] = (float)v;
+        }
+        __syncthreads();  // the fills are visible to the next chunk's window build
     }
 }
 
@@ -432,55 +403,40 @@ __global__ void speckle_apply_kernel(const float* __restrict__ f_in, float* __re
 
 }  // namespace
 
-void launch_lr_check(const float* left, const float* right, float* out_keep, float* out_work, int h, int w, int d, int scale,
-                     float thresh, cudaStream_t st, LaunchCounter& lc) {
-    dim3 grid((w + 255) / 256, h);
-    lr_check_kernel<<<grid, 256, 0, st>>>(left, right, out_keep, out_work, h, w, d, scale, thresh);
-    lc.note("lr_check_kernel");
+template <int WH, int WW>
+static void launch_lr_median_impl(const float* left, const float* right, float* out_lr, float* out_med, int* scratch_a, int* scratch_b, int h,
+                                  int w, int d, int scale, float thresh, cudaStream_t st, LaunchCounter& lc) {
+    constexpr int CHUNK = 3072;
+    const int nw = (w + 31) / 32;
+    unsigned* bitmap = reinterpret_cast<unsigned*>(scratch_a);  // [h][nw]
+    int* wordoff = scratch_a + (size_t)h * nw;                  // [h][nw]
+    int* rowoff = wordoff + (size_t)h * nw;                     // [h]
+    dim3 grid(nw, (h + LRC_TY - 1) / LRC_TY);
+    lr_classify_kernel<WH, WW><<<grid, dim3(LRC_TX, LRC_TY), 0, st>>>(left, right, out_lr, out_med, bitmap, h, w, d, scale, thresh);
+    lc.note("lr_classify_kernel");
+    constexpr size_t smem = (size_t)CHUNK * (MedianWin<WH, WW>::NB * 2 + 2 + 1);
+    auto kern = median_solve_kernel<WH, WW, CHUNK>;
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    kern<<<1, 1024, smem, st>>>(out_med, bitmap, wordoff, rowoff, scratch_b, h, w, d);
+    lc.note("median_solve_kernel");
 }
 
-void launch_median_fill(const float* src, float* f, int h, int w, int d, int win_h, int win_w, cudaStream_t st,
-                        LaunchCounter& lc) {
-    int threads = ((h + 31) / 32) * 32;
-    if (threads > 1024) threads = 1024;
-    const size_t ring_bytes = (size_t)h * 32 * sizeof(float);
-    static const bool legacy = std::getenv("SGM_B200_MEDIAN_LEGACY") != nullptr;
-    if (!legacy && win_h == 5 && win_w == 5 && h <= 1024 && (size_t)h * 65 * sizeof(float) <= 200 * 1024) {
-        // batched wavefront with 64-column rings
-        const size_t bytes = (size_t)h * 65 * sizeof(float);  // rows padded to RING + 1 floats
-        // Shape: skew 4 (2 columns per barrier), feeds 3 batches ahead, up to 2 cooperative fills per warp and column.  The
-        // time goes with the number of column steps W + K*H, not with the number of barriers (measured, K = 3 ... 10:
-        // profiles/r01_v13_summary.md), so the smallest skew that still amortises the barrier wins.
-        // SGM_B200_MEDIAN_SHAPE=6 selects the earlier skew-6 shape, =40 / =41 the per-lane-only / one-cooperative-fill forms.
-        static const int shape = [] { const char* e = std::getenv("SGM_B200_MEDIAN_SHAPE"); return e ? std::atoi(e) : 4; }();
-        auto run = [&](auto kern) {
-            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-            kern<<<1, threads, bytes, st>>>(src, f, h, w, d);
-        };
-        switch (shape) {
-            case 6: run(median_fill_batch_kernel<5, 5, 6, 64, 3, 2>); break;
-            case 40: run(median_fill_batch_kernel<5, 5, 4, 64, 3, 0>); break;
-            case 41: run(median_fill_batch_kernel<5, 5, 4, 64, 3, 1>); break;
-            default: run(median_fill_batch_kernel<5, 5, 4, 64, 3, 2>); break;
-        }
-    } else if (win_h == 5 && win_w == 5 && ring_bytes <= 200 * 1024 && h <= 2048 && d <= 65536) {
-        // shared-memory ring form (the common case); the L2 form below stays as the fallback for very tall images
-        if (h <= 1024) {
-            cudaFuncSetAttribute(median_fill_ring_kernel<5, 5, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes);
-            median_fill_ring_kernel<5, 5, 1><<<1, threads, ring_bytes, st>>>(src, f, h, w, d);
-        } else {
-            cudaFuncSetAttribute(median_fill_ring_kernel<5, 5, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes);
-            median_fill_ring_kernel<5, 5, 2><<<1, 1024, ring_bytes, st>>>(src, f, h, w, d);
-        }
-    } else if (win_h == 5 && win_w == 5)
-        median_fill_kernel<5, 5><<<1, threads, 0, st>>>(src, f, h, w, d);
-    else if (win_h == 3 && win_w == 3)
-        median_fill_kernel<3, 3><<<1, threads, 0, st>>>(src, f, h, w, d);
-    else {
+// scratch_a: >= 2 * h * ceil(w / 32) + h ints, scratch_b: >= h * w ints (the speckle filter's label / area buffers serve).
+void launch_lr_median(const float* left, const float* right, float* out_lr, float* out_med, int* scratch_a, int* scratch_b, int h, int w,
+                      int d, int scale, float thresh, int win_h, int win_w, cudaStream_t st, LaunchCounter& lc) {
+    if ((size_t)2 * h * ((w + 31) / 32) + h > (size_t)h * w) {
         lc.err = cudaErrorInvalidValue;
+        lc.failed = "launch_lr_median (image too narrow for the scratch layout)";
         return;
     }
-    lc.note("median_fill_kernel");
+    if (win_h == 5 && win_w == 5)
+        launch_lr_median_impl<5, 5>(left, right, out_lr, out_med, scratch_a, scratch_b, h, w, d, scale, thresh, st, lc);
+    else if (win_h == 3 && win_w == 3)
+        launch_lr_median_impl<3, 3>(left, right, out_lr, out_med, scratch_a, scratch_b, h, w, d, scale, thresh, st, lc);
+    else {
+        lc.err = cudaErrorInvalidValue;
+        lc.failed = "launch_lr_median (window)";
+    }
 }
 
 void launch_speckle(const float* f, float* f_out, int* labels, int* area, int h, int w, float value, int max_size,

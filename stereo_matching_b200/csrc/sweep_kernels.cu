@@ -55,59 +55,23 @@ struct SweepArgs {
     size_t vol_stride, img_stride;
 };
 
+// perf experiments (tuning build only): SweepArgs::debug & 1 skips the halo waits, & 2 the row barrier waits (WRONG results)
+__device__ __forceinline__ bool debug_skip(const SweepArgs& a, int bit) {
+#ifdef SGM_B200_TUNING
+    return (a.debug & bit) != 0;
+#else
+    (void)a;
+    (void)bit;
+    return false;
+#endif
+}
+
 template <int E>
 __device__ __forceinline__ float vec_min(const float (&v)[E]) {
     float m = v[0];
 #pragma unroll
     for (int k = 1; k < E; ++k) m = fminf(m, v[k]);
     return m;
-}
-
-// ---------------------------------------------------------------------------------------------
-// L1 (left -> right, src/SGM.cpp:82-119) and L2 (right -> left, :122-159): one warp per (row, direction, view).
-// Only 2*H*views independent lines exist, so each warp keeps PF pixels of the (contiguous) row in flight in
-// registers to cover HBM latency.
-template <int D, int PF>
-__global__ void __launch_bounds__(128) sgm_hpair_kernel(const float* __restrict__ cost, float* __restrict__ out_fwd,
-                                                        float* __restrict__ out_bwd, int h, int w, float P1, float P2,
-                                                        size_t vol_stride) {
-    using LL = LaneLayout<D>;
-    constexpr int E = LL::E;
-    const int lane = threadIdx.x & 31;
-    const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
-    if (row >= h) return;
-    const int view = blockIdx.y;
-    const bool bwd = blockIdx.z != 0;
-    const size_t base = view * vol_stride + (size_t)row * w * D;
-    const float* c = cost + base;
-    float* o = (bwd ? out_bwd : out_fwd) + base;
-    const int j0 = bwd ? w - 1 : 0, dj = bwd ? -1 : 1;
-
-    float Cb[PF][E];
-#pragma unroll
-    for (int u = 0; u < PF; ++u)
-        if (u < w) load_pixel_ro<D>(c + (size_t)(j0 + u * dj) * D, lane, Cb[u]);
-
-    float L[E];
-    float m = 0.f;
-    for (int s0 = 0; s0 < w; s0 += PF) {
-#pragma unroll
-        for (int u = 0; u < PF; ++u) {
-            const int s = s0 + u;
-            if (s < w) {
-                const int j = j0 + s * dj;
-                if (s == 0) {
-#pragma unroll
-                    for (int k = 0; k < E; ++k) L[k] = Cb[u][k];
-                    m = warp_min_f32(vec_min<E>(L));
-                } else {
-                    path_step<D>(L, Cb[u], m, lane, P1, P2);
-                }
-                store_pixel<D>(o + (size_t)j * D, lane, L);
-                if (s + PF < w) load_pixel_ro<D>(c + (size_t)(j + PF * dj) * D, lane, Cb[u]);
-            }
-        }
-    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -275,8 +239,9 @@ __device__ __forceinline__ void stg_vec(float* p, const float (&v)[LaneLayout<D>
 }
 
 // ---------------------------------------------------------------------------------------------
-// L1 / L2 again, with the row streamed through a per-warp shared-memory ring by cp.async (LDGSTS) instead of register
-// prefetch.  A deep register prefetch (16 loads in flight per warp) has to share the warp's six load scoreboards, so
+// L1 (left -> right, src/SGM.cpp:82-119) and L2 (right -> left, :122-159): one warp per (row, direction, view), the row
+// streamed through a per-warp shared-memory ring by cp.async (LDGSTS).  Only 2*H*views independent lines exist, so each
+// warp keeps PF pixels in flight.  A deep register prefetch (16 loads in flight per warp) has to share the warp's six load scoreboards, so
 // waiting for the oldest load also waits for younger ones and the effective depth collapses (measured: 1100 cycles per
 // pixel step, 2.6 TB/s, whatever the image width).  cp.async completion is tracked per commit group, so PF really
 // means PF pixels in flight, and the ring costs no registers.  Each lane copies and later reads back its own 16 bytes,
@@ -362,8 +327,11 @@ __global__ void __launch_bounds__(WARPS * 32) sgm_hpair_async_kernel(const float
 // unrolled body and every shared-memory address is base + immediate.
 constexpr int SWEEP_DOWN = 0, SWEEP_UP = 1, SWEEP_UP_KEEP = 2;
 
-template <int D, int NW, int MODE, int PATHS, int PF, int MINB, class AR>
-__global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArgs a) {
+// EDGE (compile-time copy of a warp-uniform fact): false = an interior warp — both diagonals come from shared memory and
+// neither restarts at an image border; such a warp carries none of the halo / border code (in the generic body those
+// ~35 instructions per pixel were issued predicated-off by 17 of 19 warps).  true = a block-edge or image-border warp.
+template <int D, int NW, int MODE, int PATHS, int PF, bool EDGE, class AR>
+__device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float* xmin, unsigned bar, float* sring) {
     constexpr bool UP = MODE != SWEEP_DOWN, KEEP_S = MODE == SWEEP_UP_KEEP;  // KEEP_S: also write the path sum S (debug tap)
     using LL = LaneLayout<D>;
     using HIO = HaloIO<D>;
@@ -371,31 +339,22 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
     constexpr bool DIAG = PATHS == 8;
     static_assert(NW >= 2 && PF % 2 == 0, "a block needs two columns; PF must be even");
     constexpr unsigned VEC_BYTES = D * 4, WARP_BYTES = 2 * VEC_BYTES, PAR_BYTES = NW * WARP_BYTES, MIN_PAR_BYTES = NW * 2 * 4;
-    __shared__ __align__(16) float xch[DIAG ? 2 * NW * 2 * D : 4];  // [parity][warp][0 = Pl, 1 = Pr][d]
-    __shared__ float xmin[DIAG ? 2 * NW * 2 : 1];                   // [parity][warp][0 = Pl, 1 = Pr] min of the vector
-    __shared__ __align__(8) unsigned long long bar_mem;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int blk = blockIdx.x, nblk = gridDim.x;
     const int view = a.view0 + blockIdx.y;
     const int h = a.h, w = a.w;
     const int j = blk * NW + wid;
     const int nact = min(NW, w - blk * NW);  // columns (= warps) of this block that exist
-    const unsigned bar = smem_u32(&bar_mem);
-    if (DIAG) {
-        if (threadIdx.x == 0) mbar_init(bar, nact);  // one arrival per active warp and row
-        __syncthreads();
-    }
-    if (wid >= nact) return;
 
     // ---- roles of the two diagonals of this warp ----
-    const bool swap = DIAG && wid == 0 && blk > 0;  // F = Pr (the left block waits for it), G = Pl (comes from the left block)
+    const bool swap = EDGE && DIAG && wid == 0 && blk > 0;  // F = Pr (the left block waits for it), G = Pl (comes from the left block)
     const int f_id = swap ? 1 : 0, g_id = swap ? 0 : 1;
-    const bool left_border = j == 0, right_border = j == w - 1;
+    const bool left_border = EDGE && j == 0, right_border = EDGE && j == w - 1;
     const bool f_init = swap ? right_border : left_border;  // F restarts on every row (image border on its predecessor side)
     const bool g_init = swap ? false : right_border;
     // shared-memory source warp of F; a warp whose F restarts on every row reads its own slot (valid memory, value unused)
     const int f_src_w = f_init ? wid : (swap ? wid + 1 : wid - 1);
-    const bool g_global = DIAG && (swap || (wid == nact - 1 && blk + 1 < nblk));
+    const bool g_global = EDGE && DIAG && (swap || (wid == nact - 1 && blk + 1 < nblk));
     const int g_src_w = (g_global || g_init) ? wid : wid + 1;  // shared-memory source warp of G (own slot when unused)
     const unsigned lane_off = lane * LL::CW * 4;
     const unsigned x0 = smem_u32(xch), m0 = smem_u32(xmin);
@@ -408,7 +367,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
     auto ring = [&](int b, int which) { return halo + ((size_t)(view * nblk + b) * 2 + which) * HALO_RING * HIO::SLOT_WORDS; };
     unsigned long long* f_pub = nullptr;
     const unsigned long long* g_sub = nullptr;
-    if (DIAG) {
+    if (EDGE && DIAG) {
         if (swap) f_pub = ring(blk, 1);
         else if (wid == nact - 1 && blk + 1 < nblk) f_pub = ring(blk, 0);
         if (swap) g_sub = ring(blk - 1, 0);
@@ -427,10 +386,32 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
     const ptrdiff_t pstep = UP ? -(ptrdiff_t)w : (ptrdiff_t)w;
     const size_t opix0 = view * a.img_stride + (size_t)(UP ? h - 1 : 0) * w + j;  // output pixel of sweep row 0
     WtaPick stash = {};  // lane l keeps the selection of sweep row (r & ~31) + l until the 32 rows are finished together
+    // Software-pipelined selection (up sweep): the summed vector S of row r-1 stays in registers and its warp-wide selection
+    // is issued INSIDE row r's recurrence step, between the barrier wait and the arrival.  Only the step is serial from row
+    // to row; sum, selection and stores are not, but a warp issues in order, so leaving them behind the step made every row
+    // cost the latency of both chains.  In one basic block ptxas interleaves the two independent chains.
+    float Sp[E];
+#pragma unroll
+    for (int k = 0; k < E; ++k) Sp[k] = 0.f;
+    auto select_pending = [&](int rp) {  // rp = sweep row of the vector held in Sp
+        const WtaPick pk = AR::reduce(Sp, lane);
+        if (lane == (rp & 31)) stash = pk;
+    };
+    // the scalar half (uniqueness division, parabola, stores) once per 32 rows with one lane per row
+    auto flush_rows = [&](int rlast) {
+        const int rr = (rlast & ~31) + lane;
+        if (rr <= rlast) {
+            int dd;
+            float sub;
+            wta_finish<AR::DISP>(stash, a.ratio, a.min_gap, true, dd, sub);
+            const size_t o = opix0 + (ptrdiff_t)rr * pstep;
+            a.disp[o] = (uint16_t)dd;
+            a.subpixel[o] = sub;
+        }
+    };
 
     // C / A / B rows stream through a per-warp shared-memory ring filled by cp.async: PF rows in flight per warp cost no
     // registers and are tracked per commit group (a deep register prefetch would alias the load scoreboards).
-    extern __shared__ __align__(16) float sring[];  // [NW][PF][3][D]
     constexpr unsigned SLOT_BYTES = 3 * VEC_BYTES;
     const unsigned rbase = smem_u32(sring) + (unsigned)wid * PF * SLOT_BYTES + lane_off;
     auto fetch = [&](int slot) {
@@ -471,7 +452,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                 // round trip overlaps the barrier wait and the F step; the tags are checked where the vector is needed
                 unsigned long long peeked[E];
                 float Gin[E];
-                const bool peek_ok = DIAG && g_global && r > 0 && !dead && !(a.debug & 1);
+                const bool peek_ok = EDGE && DIAG && g_global && r > 0 && !dead && !debug_skip(a, 1);
                 bool got = false;
                 if (peek_ok) {
                     if (early_ok) got = HIO::accept(early, Gin, tag - 1u);
@@ -479,7 +460,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                 }
                 asm volatile("cp.async.wait_group %0;" ::"n"(PF - 1) : "memory");  // this row's C / A / B have landed
                 lds_pixel<D>(rbase + u * SLOT_BYTES, C);
-                if (DIAG && r > 0 && !(a.debug & 2)) mbar_wait(bar, par ^ 1u, a.error);  // every warp's row r-1 vectors are in shared memory
+                if (DIAG && r > 0 && !debug_skip(a, 2)) mbar_wait(bar, par ^ 1u, a.error);  // every warp's row r-1 vectors are in shared memory
                 // ---- the three recurrences of this pixel (P[0] = F, P[1] = V, P[2] = G) ----
                 // F, V and G only depend on the previous row, not on each other, so they advance together
                 // (path_step_n) unless G has to wait for a neighbouring block: then F goes first and is published,
@@ -499,6 +480,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                     }
                 } else if (!DIAG) {
                     AR::step(V, C, mV, lane, a.P1, a.P2);
+                    if (UP) select_pending(r - 1);
                 } else {
                     float P[3][E], mP[3];
                     // previous-row vectors: F and (unless it comes from another block) G from shared memory
@@ -512,6 +494,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                         lds_pixel<D>(g_src + (par ^ 1u) * PAR_BYTES, P[2]);
                         mP[2] = lds_f32(gm_src + (par ^ 1u) * MIN_PAR_BYTES);
                         AR::template step_n<3>(P, C, mP, lane, a.P1, a.P2);
+                        if (UP) select_pending(r - 1);
                     } else {
                         // block-edge warp: F first (a neighbouring block is waiting for it), then V and G together
                         float P0[1][E], m0[1] = {mP[0]};
@@ -524,6 +507,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                             m0[0] = AR::vmin(C);
                         }
                         if (f_pub) HIO::publish(f_pub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, P0[0], tag);
+                        if (UP) select_pending(r - 1);  // the neighbour's vector may still be on its way: use the time
                         float P12[2][E], m12[2];
                         if (peek_ok && !got && !HIO::accept(peeked, Gin, tag - 1u) &&
                             !HIO::consume(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, Gin, tag - 1u)) {
@@ -576,7 +560,7 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                 if (DIAG) {
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar);  // this warp's row r vectors are published
-                    early_ok = g_global && r + 1 < h && !dead && !(a.debug & 1);
+                    early_ok = EDGE && g_global && r + 1 < h && !dead && !debug_skip(a, 1);
                     if (early_ok) HIO::peek(g_sub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, early);
                 }
                 // ---- outputs (overlap the other warps' arrival) ----
@@ -614,27 +598,44 @@ __global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArg
                         stg_vec<D>(os, S);
                         os += rstep;
                     }
-                    // the warp-wide half of the selection now; the scalar half (uniqueness division, parabola, stores)
-                    // once per 32 rows with one lane per row instead of 32 lanes repeating the same arithmetic
-                    const WtaPick pk = AR::reduce(S, lane);
-                    if (lane == (r & 31)) stash = pk;
-                    if ((r & 31) == 31 || r == h - 1) {
-                        const int rr = (r & ~31) + lane;
-                        if (rr <= r) {
-                            int dd;
-                            float sub;
-                            wta_finish<AR::DISP>(stash, a.ratio, a.min_gap, true, dd, sub);
-                            const size_t o = opix0 + (ptrdiff_t)rr * pstep;
-                            a.disp[o] = (uint16_t)dd;
-                            a.subpixel[o] = sub;
-                        }
-                    }
+                    // selection: see select_pending (runs inside the next row's step); here only the rare flush of 32 rows
+                    if (r > 0 && ((r - 1) & 31) == 31) flush_rows(r - 1);
+#pragma unroll
+                    for (int k = 0; k < E; ++k) Sp[k] = S[k];
                 }
                 if (r + PF < h) fetch(u);  // slot u is free: this lane has read its own bytes back
                 asm volatile("cp.async.commit_group;" ::: "memory");
             }
         }
     }
+    if (UP) {  // drain the pipeline: the last row's selection and the rows still stashed
+        select_pending(h - 1);
+        flush_rows(h - 1);
+    }
+}
+
+template <int D, int NW, int MODE, int PATHS, int PF, int MINB, class AR>
+__global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArgs a) {
+    constexpr bool DIAG = PATHS == 8;
+    __shared__ __align__(16) float xch[DIAG ? 2 * NW * 2 * D : 4];  // [parity][warp][0 = Pl, 1 = Pr][d]
+    __shared__ float xmin[DIAG ? 2 * NW * 2 : 1];                   // [parity][warp][0 = Pl, 1 = Pr] min of the vector
+    __shared__ __align__(8) unsigned long long bar_mem;
+    extern __shared__ __align__(16) float sring[];  // [NW][PF][3][D]
+    const int wid = threadIdx.x >> 5, blk = blockIdx.x;
+    const int nact = min(NW, a.w - blk * NW);  // columns (= warps) of this block that exist
+    const unsigned bar = smem_u32(&bar_mem);
+    if (DIAG) {
+        if (threadIdx.x == 0) mbar_init(bar, nact);  // one arrival per active warp and row
+        __syncthreads();
+    }
+    if (wid >= nact) return;
+    const int j = blk * NW + wid;
+    // block-edge warps (they exchange with a neighbouring block) and image-border columns take the general body
+    const bool edge = DIAG && (wid == 0 || wid == nact - 1 || j == 0 || j == a.w - 1);
+    if (edge)
+        sweep_body<D, NW, MODE, PATHS, PF, true, AR>(a, xch, xmin, bar, sring);
+    else
+        sweep_body<D, NW, MODE, PATHS, PF, false, AR>(a, xch, xmin, bar, sring);
 }
 
 constexpr int SWEEP_NW = 8;  // smallest block width in columns (sizes the halo ring)
@@ -689,14 +690,16 @@ int sweep_capacity(int device) {
 // of disparities).
 template <int D, int PATHS, class CFG, class AR = F32Arith<D>>
 bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
-    constexpr bool PACKED = AR::DISP != D;
     const int nblk = (a.w + CFG::NW - 1) / CFG::NW;
     int views_per_launch = a.views;
     if (PATHS == 8) {
         int device = 0;
         cudaGetDevice(&device);
         const int cap = sweep_capacity<D, PATHS, CFG, AR>(device);
-        static const bool split = std::getenv("SGM_B200_SWEEP_SPLIT_VIEWS") != nullptr;
+        bool split = false;  // one view per launch: taken when both views do not fit a resident grid (1080p); forced in tuning builds
+#ifdef SGM_B200_TUNING
+        split = std::getenv("SGM_B200_SWEEP_SPLIT_VIEWS") != nullptr;
+#endif
         if (nblk * a.views > cap || split) views_per_launch = 1;
         if (nblk > cap) return false;  // image too wide for a resident row-synchronous sweep: caller falls back to line walkers
     }
@@ -704,11 +707,7 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
     {
         constexpr int PFH = (LaneLayout<D>::E >= 8) ? 8 : 16, HW = 4;
         constexpr size_t ring_bytes = (size_t)HW * PFH * D * sizeof(float);  // 32 KB for D >= 128
-        static const bool legacy = std::getenv("SGM_B200_HPAIR_LEGACY") != nullptr;
-        if (legacy && !PACKED)
-            sgm_hpair_kernel<D, PFH><<<dim3((a.h + 3) / 4, a.views, 2), 128, 0, st>>>(a.cost, a.acc_a, a.acc_b, a.h, a.w, a.P1, a.P2, vol);
-        else
-            sgm_hpair_async_kernel<D, PFH, HW, AR><<<dim3((a.h + HW - 1) / HW, a.views, 2), HW * 32, ring_bytes, st>>>(
+        sgm_hpair_async_kernel<D, PFH, HW, AR><<<dim3((a.h + HW - 1) / HW, a.views, 2), HW * 32, ring_bytes, st>>>(
                 a.cost, a.acc_a, a.acc_b, a.h, a.w, a.P1, a.P2, vol);
         lc.note("sgm_hpair_kernel");
     }
@@ -722,10 +721,13 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
     sa.subpixel = a.subpixel;
     sa.halo = a.halo;
     sa.error = a.error;
+    sa.debug = 0;
+#ifdef SGM_B200_TUNING
     {
         static const int dbg = [] { const char* e = std::getenv("SGM_B200_SWEEP_DEBUG"); return e ? std::atoi(e) : 0; }();
         sa.debug = dbg;
     }
+#endif
     sa.h = a.h;
     sa.w = a.w;
     sa.P1 = a.P1;
@@ -769,6 +771,7 @@ struct DefaultCfg<128> {
 template <int D>
 bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
     if (a.paths != 8) return fused_impl<D, 4, typename DefaultCfg<D>::type>(a, st, lc);
+#ifdef SGM_B200_TUNING
     if constexpr (D == 128) {
         static const int cfg = [] {
             const char* e = std::getenv("SGM_B200_SWEEP_CFG");
@@ -791,6 +794,7 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
             default: break;
         }
     }
+#endif
     if constexpr (D <= 128) {
         // Automatic shape: when the default would put two blocks on some SMs and one on others (rows advance in
         // lock-step, so the crowded SMs set the pace), prefer one wide block per SM with a few SMs left over for the
@@ -817,6 +821,7 @@ bool fused_dispatch_packed(const AggregateArgs& a0, cudaStream_t st, LaunchCount
     memcpy(&a.P2, &P2w, sizeof(float));
     using AR = S16x2Arith<DW>;
     if (a.paths != 8) return fused_impl<DW, 4, typename DefaultCfg<DW>::type, AR>(a, st, lc);
+#ifdef SGM_B200_TUNING
     static const int cfg = [] {
         const char* e = std::getenv("SGM_B200_ISWEEP_CFG");
         return e ? std::atoi(e) : 0;
@@ -830,6 +835,7 @@ bool fused_dispatch_packed(const AggregateArgs& a0, cudaStream_t st, LaunchCount
         case 6: return fused_impl<DW, 8, SweepCfg<9, 4, 2>, AR>(a, st, lc);
         default: break;
     }
+#endif
     int device = 0, sms = 0;
     cudaGetDevice(&device);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);

@@ -3,7 +3,9 @@
 // :104 get_disp(); :107 show_disp(debug_view)) and dumps the results for tests/test_host_shell.py.
 //
 //   host_shell_main <sgm|bm> H W SCALE D in_left.raw in_right.raw [sky_l.raw sky_r.raw|- -] out_prefix
+//   host_shell_main bench <sgm|bm> H W SCALE D in_left.raw in_right.raw FRAMES     (bench.py's `blocking` leg: one JSON line)
 // TEST INFRASTRUCTURE.
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -34,7 +36,41 @@ static void write_raw(const std::string& path, const Mat& m, size_t elem) {
     std::fclose(f);
 }
 
+// Blocking frame loop exactly as node.cpp:93,104 runs it: process(l, r) then get_disp(), one frame at a time.
+static int bench_main(int argc, char** argv) {
+    if (argc != 10) return 2;
+    const bool bm = std::strcmp(argv[2], "bm") == 0;
+    const int h = std::atoi(argv[3]), w = std::atoi(argv[4]), s = std::atoi(argv[5]), d = std::atoi(argv[6]);
+    const int frames = std::atoi(argv[9]);
+    Mat img_l(h, w, CV_8UC1), img_r(h, w, CV_8UC1);
+    if (!read_raw(argv[7], img_l) || !read_raw(argv[8], img_r) || frames < 1) return 3;
+    SolverPtr sv;
+    if (bm)
+        sv = std::make_shared<BM>(h, w, s, d);
+    else
+        sv = std::make_shared<SGM>(h, w, s, d);
+    FILE* quiet = std::freopen("/dev/null", "w", stdout);  // the shells print "no sky mask" per frame like the reference
+    (void)quiet;
+    std::vector<double> ms((size_t)frames);
+    double checksum = 0.0;
+    for (int k = 0; k < 5; ++k) sv->process(img_l, img_r);  // warm-up
+    const double t_begin = get_cur_ms();
+    for (int k = 0; k < frames; ++k) {
+        const double t0 = get_cur_ms();
+        sv->process(img_l, img_r);
+        const Mat& f = sv->get_disp();
+        checksum += f.ptr<float>(h / s / 2)[w / s / 2];
+        ms[(size_t)k] = get_cur_ms() - t0;
+    }
+    const double total = get_cur_ms() - t_begin;
+    std::sort(ms.begin(), ms.end());
+    std::fprintf(stderr, "{\"blocking_fps\": %.2f, \"latency_ms_median\": %.4f, \"latency_ms_p90\": %.4f, \"frames\": %d, \"checksum\": %.3f}\n",
+                 1e3 * frames / total, ms[(size_t)frames / 2], ms[(size_t)(frames * 9) / 10], frames, checksum);
+    return 0;
+}
+
 int main(int argc, char** argv) {
+    if (argc >= 2 && std::strcmp(argv[1], "bench") == 0) return bench_main(argc, argv);
     if (argc != 11) {
         std::fprintf(stderr, "usage: %s <sgm|bm> H W SCALE D left.raw right.raw sky_l.raw|- sky_r.raw|- out_prefix\n", argv[0]);
         return 2;

@@ -14,7 +14,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
-from oracle import restate  # noqa: E402
+from oracle import refbind, restate  # noqa: E402
 from stereo_matching_b200 import synth  # noqa: E402
 
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -34,6 +34,15 @@ def run_case(c):
     for v in (0, 1):  # the claim the mode rests on: the float path computes integers, the 16-bit form agrees
         Si = restate.aggregate_u16(out["cost_raw"][v].astype(np.uint16), 10, 100, 8)
         assert np.array_equal(Si.astype(np.float32), out["S"][v]), "16-bit restatement differs from the float restatement"
+    # direct pin where the reference can run it (scale 1): its own sources compiled with COST_WIN_H = COST_WIN_W = 1
+    # (make -C oracle ref_nofilter) must give the same path sums, disparities and final image
+    if s == 1 and refbind.available("nofilter"):
+        with refbind.use("nofilter"):
+            refbind.set_threads(1)
+            ref = refbind.process("sgm", L, R, 1, c["d"], want_cost=True)
+        assert np.array_equal(ref["cost_last"], out["S"][1]) and np.array_equal(ref["disp"], out["disp"][0])
+        assert np.array_equal(ref["disp_beta"], out["disp"][1]) and np.array_equal(ref["fdisp"].view(np.uint32), out["f_final"].view(np.uint32))
+        c = dict(c, pinned_by="oracle/_ref/libsgm_ref_nofilter.so (reference sources, COST_WIN_H = COST_WIN_W = 1)")
     f = out["f_final"]
     rec = dict(c)
     rec["hashes"] = dict(left=H(L), right=H(R), cost_l=H(out["cost_hv"][0]), cost_r=H(out["cost_hv"][1]), S_l=H(out["S"][0]),

@@ -82,3 +82,17 @@ def test_no_cpu_fallback_without_a_device(lib):
     with pytest.raises(capi.SgmError) as e:
         capi.SGM(64, 64, 1, 32)
     assert e.value.code == 3 and "no CPU path" in str(e.value)
+    # the frame-stream runner is built on the same handles: same answer, and its argument checks come before any device call
+    with pytest.raises(capi.SgmError) as e:
+        capi.Stream(64, 64, 1, 32, devices=(0,), inflight=2)
+    assert e.value.code == 3 and "no CPU path" in str(e.value)
+    with pytest.raises(capi.SgmError) as e:
+        capi.Stream(64, 64, 1, 32, devices=(0,), inflight=0)
+    assert e.value.code == 1
+    # the allocation-free speckle entry point: size limit and argument checks need no device either
+    with pytest.raises(capi.SgmError) as e:
+        capi.speckle_filter_static(1, 1, 2048, 1025, 65.0)
+    assert e.value.code == 2
+    with pytest.raises(capi.SgmError) as e:
+        capi.speckle_filter_static(1, 1, 64, 64, 65.0)
+    assert e.value.code == 3

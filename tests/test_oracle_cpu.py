@@ -128,6 +128,40 @@ def test_integer_restatement_equals_float_restatement_without_cost_filter(h, w, 
         assert np.array_equal(Si.astype(np.float32), S)
 
 
+@pytest.mark.skipif(not refbind.available("nofilter"), reason="oracle/_ref/libsgm_ref_nofilter.so not built")
+@pytest.mark.parametrize("h,w,d,noise", [(96, 160, 64, 6), (64, 300, 128, 25), (97, 161, 32, 60)])
+def test_restatement_without_cost_filter_against_reference_nofilter(h, w, d, noise):
+    # the DIRECT pin of the integer / DPX mode's oracle: the reference's own sources compiled with COST_WIN_H = COST_WIN_W = 1
+    # (make -C oracle ref_nofilter) against the restatement with box_w = box_h = 1, tap by tap, and its 16-bit integer form
+    L, R, _ = synth.random_dot_pair(h, w, seed=h * 5 + d, bg=3, fg=max(4, min(17, d // 2)), noise=noise)
+    mine = restate.process(L, R, 1, d, "sgm", taps=restate.ALL_TAPS, box_w=1, box_h=1)
+    with refbind.use("nofilter"):
+        refbind.set_threads(1)
+        ref = refbind.process("sgm", L, R, 1, d, want_cost=True)
+        st = [refbind.stages("sgm", L, R, 1, d, beta=b) for b in (False, True)]
+    assert bits_equal(st[0]["cost_hv"], st[0]["cost_raw"])                      # the filter really is off in that build
+    assert bits_equal(mine["cost_hv"][0], st[0]["cost_hv"]) and bits_equal(mine["cost_hv"][1], st[1]["cost_hv"])
+    assert bits_equal(mine["S"][1], ref["cost_last"])
+    assert n_diff(mine["disp"][0], ref["disp"]) == 0 and n_diff(mine["disp"][1], ref["disp_beta"]) == 0
+    assert bits_equal(mine["fsub"][1], ref["fdisp_beta"]) and bits_equal(mine["f_final"], ref["fdisp"])
+    Si = restate.aggregate_u16(st[1]["cost_hv"].astype(np.uint16), 10, 100, 8)  # 16-bit form on the REFERENCE's volume
+    assert np.array_equal(Si.astype(np.float32), ref["cost_last"])
+
+
+@pytest.mark.skipif(not refbind.available("nofilter"), reason="oracle/_ref/libsgm_ref_nofilter.so not built")
+def test_integer_mode_golden_equals_reference_nofilter(golden_integer):
+    # tests/golden/kat_hashes_integer.json at KITTI size against the reference built without its cost filter
+    c = golden_integer["kitti_int_d64_clean"]
+    L, R, _ = synth.random_dot_pair(c["h"], c["w"], seed=c["seed"], bg=c["bg"], fg=c["fg"], noise=c["noise"])
+    with refbind.use("nofilter"):
+        refbind.set_threads(1)
+        ref = refbind.process("sgm", L, R, 1, c["d"], want_cost=True)
+    want = c["hashes"]
+    assert H(ref["cost_last"]) == want["S_r"] and H(ref["disp"].astype(np.uint16)) == want["disp"]
+    assert H(ref["disp_beta"].astype(np.uint16)) == want["disp_beta"] and H(ref["fdisp_beta"]) == want["fsub_r"]
+    assert H(ref["fdisp"]) == want["f_final"]
+
+
 def test_integer_mode_golden_is_reproducible(golden_integer):
     # tests/golden/kat_hashes_integer.json must be what the restatement (window 1x1) produces today
     c = golden_integer["kitti_int_d64_scale2"]
@@ -152,6 +186,16 @@ def test_fullsize_golden_is_reproducible(golden_fullsize, name):
     assert H(out["disp"][0]) == want["disp_l"] and H(out["disp"][1]) == want["disp_r"] and H(out["fsub"][1]) == want["fsub_r"]
     assert H(out["f_lr"]) == want["f_lr"] and H(out["f_median"]) == want["f_median"] and H(out["f_final"]) == want["f_final"]
     assert int((out["f_final"] <= c["d"] - 1).sum()) == c["stats"]["valid"]
+
+
+@pytest.mark.skipif(not refbind.available(), reason="compiled reference (oracle/_ref) not built")
+@pytest.mark.parametrize("kind,wh,ww,scale", [("ssd", 7, 9, 1), ("ssd", 9, 9, 2), ("ssd", 3, 5, 1), ("ct", 7, 9, 1), ("ct", 7, 9, 2), ("ct", 3, 3, 1)])
+def test_window_cost_restatement_against_reference_functions(kind, wh, ww, scale):
+    # SSD() / CT() of the reference (src/cost.cpp:33-96), called for every (pixel, d) by the harness, against the numpy
+    # restatement the GPU tests use as their checker
+    L, R, _ = synth.random_dot_pair(24, 45, seed=5 + wh, bg=2, fg=6, noise=20)
+    want = refbind.cost_volume(kind, L, R, 20, wh, ww, scale)
+    assert bits_equal(restate.window_cost_volume(kind, L, R, 20, wh, ww, scale), want)
 
 
 def test_widened_restatement_runs_d256():

@@ -285,6 +285,91 @@ def test_dense_sad_entry_point_vs_oracle():
         assert bits_equal(capi.cost_volume_sad(L, R, 32, wh, ww), want), (wh, ww)
 
 
+def test_median_3x3_window_vs_oracle():
+    # sgm_create accepts MEDIAN_FILTER_H/W = 3 (inc/Solver.h:17-18 are compile-time constants of the reference; the
+    # restatement takes them as parameters): the other instantiation of the median kernels
+    L, R, _ = synth.random_dot_pair(97, 161, seed=15, bg=5, fg=17, noise=60)
+    _check_sgm_against_restatement(L, R, 1, 64, median_h=3, median_w=3)
+    L, R, _ = synth.random_dot_pair(120, 200, seed=16, bg=4, fg=12, noise=30)
+    want = restate.process(L, R, 1, 64, "bm_sad", median_h=3, median_w=3)
+    bm = capi.BMSad(120, 200, 1, 64, median_h=3, median_w=3)
+    assert bits_equal(bm.process(L, R).tap("median"), want["f_median"]) and bits_equal(bm.get_disp(), want["f_final"])
+    bm.close()
+
+
+@pytest.mark.parametrize("algo,noise", [("sgm", 200), ("bm_sad", 120), ("bm", 120)])
+def test_median_many_candidates_spans_several_chunks(algo, noise):
+    # very heavy noise leaves far more fillable holes (8e3 for SGM, 5e4 - 7e4 for block matching: a third of the frame is
+    # invalid) than one shared-memory chunk of the median solver holds (3072): chunks are resolved in raster order and later
+    # chunks read the earlier ones' fills; block matching also has dependency chains hundreds of holes deep
+    h, w, d = 400, 1000, 64
+    L, R, _ = synth.random_dot_pair(h, w, seed=23, bg=6, fg=25, noise=noise)
+    want = restate.process(L, R, 1, d, algo)
+    filled = int((want["f_median"].view(np.uint32) != want["f_lr"].view(np.uint32)).sum())
+    assert filled > 2 * 3072, f"only {filled} holes were filled: the case does not span several chunks"
+    sv = {"sgm": capi.SGM, "bm_sad": capi.BMSad, "bm": capi.BM}[algo](h, w, 1, d)
+    sv.process(L, R)
+    assert bits_equal(sv.tap("lr"), want["f_lr"]) and bits_equal(sv.tap("median"), want["f_median"])
+    assert bits_equal(sv.get_disp(), want["f_final"])
+    sv.close()
+
+
+def test_dense_sad_generic_kernel_vs_oracle():
+    # disparity counts that are not a power of two (and very wide windows) take the per-row SAD kernel instead of the banded one
+    L, R, _ = synth.random_dot_pair(40, 70, seed=2, bg=3, fg=7, noise=12)
+    for d, wh, ww in ((24, 9, 9), (40, 5, 7), (32, 3, 27)):
+        want = restate.process(L, R, 1, 64, "bm_sad", taps=("cost_raw",), sad_h=wh, sad_w=ww)["cost_raw"][0][:, :, :d]
+        assert bits_equal(capi.cost_volume_sad(L, R, d, wh, ww), np.ascontiguousarray(want)), (d, wh, ww)
+
+
+@pytest.mark.parametrize("kind,wh,ww,scale,d", [("ssd", 7, 9, 1, 32), ("ssd", 9, 9, 2, 24), ("ssd", 3, 5, 1, 64), ("ssd", 15, 17, 1, 16),
+                                                ("ct", 7, 9, 1, 32), ("ct", 7, 9, 2, 24), ("ct", 3, 3, 1, 64), ("ct", 5, 11, 1, 40)])
+def test_dense_ssd_and_ct_volumes_vs_oracle(kind, wh, ww, scale, d):
+    # SSD / CT of inc/cost.h:8-9 as dense device volumes (row A12): checker = the numpy restatement (pinned against the
+    # reference's own functions on the CPU) and, where the compiled reference travelled, those functions themselves
+    L, R, _ = synth.random_dot_pair(41, 77, seed=7 + wh + d, bg=3, fg=9, noise=25)
+    got = capi.cost_volume(kind, L, R, d, wh, ww, scale)
+    assert bits_equal(got, restate.window_cost_volume(kind, L, R, d, wh, ww, scale)), (kind, wh, ww, scale, d)
+    if refbind.available():
+        assert bits_equal(got, refbind.cost_volume(kind, L, R, d, wh, ww, scale))
+
+
+def test_dense_ssd_and_ct_reject_oversized_windows():
+    z = np.zeros((32, 32), np.uint8)
+    with pytest.raises(capi.SgmError) as e:
+        capi.cost_volume("ssd", z, z, 16, 17, 17)   # 289 pixels * 255^2 >= 2^24: float accumulation would round
+    assert e.value.code == 2
+    with pytest.raises(capi.SgmError) as e:
+        capi.cost_volume("ct", z, z, 16, 9, 9)      # 80 taps do not fit the reference's 64-bit strings
+    assert e.value.code == 2
+
+
+def test_device_resident_pitched_sky_masks():
+    # sgm_enqueue_device with sky masks whose row pitch is larger than the width (densified on the device), and with the
+    # caller's left image overwritten right after sgm_wait (the engine keeps its own copy for sgm_point_cloud)
+    torch = pytest.importorskip("torch")
+    h, w, d = 120, 200, 64
+    L, R, _ = synth.random_dot_pair(h, w, seed=31, bg=5, fg=17, noise=15)
+    sl, sr = synth.sky_masks(h, w, 0.3)
+    want = restate.process(L, R, 1, d, "sgm", sl, sr)["f_final"]
+    tl, tr = torch.from_numpy(L).cuda(), torch.from_numpy(R).cuda()
+    pitch = w + 56
+    tsl, tsr = torch.zeros((h, pitch), dtype=torch.uint8, device="cuda"), torch.zeros((h, pitch), dtype=torch.uint8, device="cuda")
+    tsl[:, :w], tsr[:, :w] = torch.from_numpy(sl).cuda(), torch.from_numpy(sr).cuda()
+    tsl[:, w:], tsr[:, w:] = 255, 255            # padding bytes that must not be read as mask
+    torch.cuda.synchronize()
+    sv = capi.SGM(h, w, 1, d)
+    sv.enqueue_device(tl.data_ptr(), w, tr.data_ptr(), w, tsl.data_ptr(), pitch, tsr.data_ptr(), pitch)
+    sv.wait()
+    assert bits_equal(sv.get_disp(), want)
+    xyz0, int0 = sv.point_cloud(718.856, 718.856, 607.1928, 185.2157)
+    tl.zero_()                                    # the caller reuses its buffer
+    torch.cuda.synchronize()
+    xyz1, int1 = sv.point_cloud(718.856, 718.856, 607.1928, 185.2157)
+    assert np.array_equal(int0, int1) and np.array_equal(xyz0, xyz1) and int0.any()
+    sv.close()
+
+
 def test_strided_inputs_repeat_and_two_handles():
     h, w, d = 64, 160, 32
     L, R, _ = synth.random_dot_pair(h, w, seed=9, bg=4, fg=11, noise=10)
