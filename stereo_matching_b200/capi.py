@@ -11,7 +11,9 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsgm_b200.so")
+# SGM_B200_LIBRARY (read here, in the Python test harness, never by the C library): load another build of the library, e.g. the
+# tuning build libsgm_b200_tuning.so with its experiment knobs
+LIB_PATH = os.environ.get("SGM_B200_LIBRARY") or os.path.join(HERE, "libsgm_b200.so")
 
 ALGO_SGM, ALGO_BM, ALGO_BM_SAD = 0, 1, 2
 FLAG_KEEP_VOLUMES, FLAG_STAGE_TIMING, FLAG_LINE_WALKERS, FLAG_INTEGER, FLAG_HOST_TAPS = 1, 2, 4, 8, 16

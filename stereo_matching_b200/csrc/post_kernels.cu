@@ -2,6 +2,7 @@
 //
 // Replaces src/SGM.cpp:803-818 and Solver::post_filter (src/Solver.cpp:600-635, speckle_filter_new
 // :514-566) of the reference, with the reference's serial (single-thread) semantics.
+#include <cstdio>
 #include <cstdlib>
 #include <mutex>
 
@@ -102,46 +103,68 @@ __global__ void __launch_bounds__(LRC_TX* LRC_TY) lr_classify_kernel(const float
 //   2. in chunks of CHUNK candidates (raster order): every candidate's window goes to shared memory as 16-bit entries —
 //      a literal value (already final: a non-hole, a hole that can never be filled, or a fill of an earlier chunk) or a
 //      REFERENCE to an earlier candidate of the same chunk;
-//   3. rounds: a candidate whose references are all resolved takes its median (or stays invalid); one that can no longer
-//      reach half a window of valid values is dropped early.  The first unresolved candidate in raster order has no
-//      unresolved reference, so every round resolves something; the number of rounds is the depth of the dependency DAG.
+//   3. warps resolve groups of 32 consecutive candidates (no block barrier): a candidate whose references are all resolved
+//      takes its median (the warp evaluates it together), one that can no longer reach half a window of valid values is
+//      dropped early.  The first unresolved candidate in raster order has no unresolved reference, so there is always
+//      progress.
 // Window entries: 0 .. 0x7ffe literal (int)value (the reference truncates to int, src/Solver.cpp:619), 0x7fff invalid,
 // 0x8000 | k reference to candidate k of the chunk.  val[k]: 0xffff unresolved, else like a literal.
 constexpr unsigned short MED_INVALID = 0x7fff, MED_UNRESOLVED = 0xffff;
 
 template <int WH, int WW, int CHUNK>
-__global__ void __launch_bounds__(1024) median_solve_kernel(float* f, const unsigned* __restrict__ bitmap, int* wordoff, int* rowoff, int* list,
+__global__ void __launch_bounds__(512) median_solve_kernel(float* f, const unsigned* __restrict__ bitmap, int* wordoff, int* rowoff, int* list,
                                                             int h, int w, int d) {
     using MW = MedianWin<WH, WW>;
     constexpr int NB = MW::NB, NC = MW::NC, HALF = MW::NWIN / 2;
     extern __shared__ __align__(16) unsigned char msm[];
-    unsigned short* win = reinterpret_cast<unsigned short*>(msm);            // [CHUNK][NB]
-    unsigned short* val = win + (size_t)CHUNK * NB;                            // [CHUNK]
+    constexpr int NBP = NB + 2;  // row pitch: NB window entries + the reference mask + pad = an odd number of 32-bit words (no bank collisions between rows)
+    unsigned short* win = reinterpret_cast<unsigned short*>(msm);            // [CHUNK][NBP]
+    unsigned short* val = win + (size_t)CHUNK * NBP;                           // [CHUNK]
     unsigned char* litv = reinterpret_cast<unsigned char*>(val + CHUNK);       // [CHUNK] literal valid entries of the window
     __shared__ int wsum[32];
     __shared__ int total_s;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nwarp = blockDim.x >> 5;
     const int nw = (w + 31) / 32;
     const float vmax = (float)(d - 1);
+#ifdef SGM_B200_TUNING
+    long long tstamp[8];
+    int nstamp = 0;
+#define MED_STAMP() do { __syncthreads(); if (nstamp < 8) tstamp[nstamp++] = clock64(); } while (0)
+#else
+#define MED_STAMP() do { } while (0)
+#endif
+    MED_STAMP();
 
     // ---- 1a. per-row counts and row-relative word offsets ----
-    for (int i = wid; i < h; i += nwarp) {
-        int total = 0;
+    // (one block does all of this, so global latency is hidden by keeping RB rows in flight per warp)
+    constexpr int RB = 4;
+    for (int i0 = wid * RB; i0 < h; i0 += nwarp * RB) {
+        int total[RB];
+#pragma unroll
+        for (int r = 0; r < RB; ++r) total[r] = 0;
         for (int jw0 = 0; jw0 < nw; jw0 += 32) {
             const int jw = jw0 + lane;
-            const int c = jw < nw ? __popc(bitmap[(size_t)i * nw + jw]) : 0;
-            int inc = c;
+            int c[RB];
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int x = __shfl_up_sync(FULL_MASK, inc, o);
-                if (lane >= o) inc += x;
+            for (int r = 0; r < RB; ++r) c[r] = (jw < nw && i0 + r < h) ? __popc(bitmap[(size_t)(i0 + r) * nw + jw]) : 0;
+#pragma unroll
+            for (int r = 0; r < RB; ++r) {
+                int inc = c[r];
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int x = __shfl_up_sync(FULL_MASK, inc, o);
+                    if (lane >= o) inc += x;
+                }
+                if (jw < nw && i0 + r < h) wordoff[(size_t)(i0 + r) * nw + jw] = total[r] + inc - c[r];
+                total[r] += __shfl_sync(FULL_MASK, inc, 31);
             }
-            if (jw < nw) wordoff[(size_t)i * nw + jw] = total + inc - c;
-            total += __shfl_sync(FULL_MASK, inc, 31);
         }
-        if (lane == 0) rowoff[i] = total;
+#pragma unroll
+        for (int r = 0; r < RB; ++r)
+            if (lane == 0 && i0 + r < h) rowoff[i0 + r] = total[r];
     }
     __syncthreads();
+    MED_STAMP();
     // ---- 1b. exclusive scan of the row counts (contiguous rows per thread, then the classic two-level scan) ----
     {
         const int per = (h + (int)blockDim.x - 1) / (int)blockDim.x, r0 = tid * per, r1 = min(h, r0 + per);
@@ -176,30 +199,52 @@ __global__ void __launch_bounds__(1024) median_solve_kernel(float* f, const unsi
     }
     __syncthreads();
     const int ncand = total_s;
+    MED_STAMP();
     if (ncand == 0) return;
     // ---- 1c. absolute word offsets and the candidate list ----
-    for (int i = wid; i < h; i += nwarp) {
-        const int base = rowoff[i];
+    for (int i0 = wid * RB; i0 < h; i0 += nwarp * RB) {
+        int base[RB];
+#pragma unroll
+        for (int r = 0; r < RB; ++r) base[r] = i0 + r < h ? rowoff[i0 + r] : 0;
         for (int jw = lane; jw < nw; jw += 32) {
-            const size_t wi = (size_t)i * nw + jw;
-            int k = wordoff[wi] + base;
-            wordoff[wi] = k;
-            unsigned word = bitmap[wi];
-            while (word) {
-                const int bit = __ffs(word) - 1;
-                word &= word - 1;
-                list[k++] = i * w + jw * 32 + bit;
+            int k[RB];
+            unsigned word[RB];
+#pragma unroll
+            for (int r = 0; r < RB; ++r) {
+                const bool in = i0 + r < h;
+                const size_t wi = (size_t)(in ? i0 + r : 0) * nw + jw;
+                k[r] = in ? wordoff[wi] : 0;
+                word[r] = in ? bitmap[wi] : 0u;
+            }
+#pragma unroll
+            for (int r = 0; r < RB; ++r) {
+                if (i0 + r >= h) continue;
+                int kk = k[r] + base[r];
+                wordoff[(size_t)(i0 + r) * nw + jw] = kk;
+                for (unsigned wd = word[r]; wd; wd &= wd - 1) list[kk++] = (i0 + r) * w + jw * 32 + (__ffs(wd) - 1);
             }
         }
     }
     __syncthreads();
+    MED_STAMP();
 
     // ---- 2 / 3. chunks of candidates ----
     for (int base = 0; base < ncand; base += CHUNK) {
         const int cn = min(CHUNK, ncand - base);
         for (int c = tid; c < cn; c += blockDim.x) {
             const int p = list[base + c], i = p / w, j = p - i * w;
+            // all loads of the window first (independent, so they overlap), decisions afterwards
+            float fv[NB];
+            unsigned bw[NC];
+#pragma unroll
+            for (int t = 0; t < NB; ++t) {
+                int a, b;
+                MW::offset(t, a, b);
+                fv[t] = f[(size_t)(i + a) * w + (j + b)];
+                if (t < NC) bw[t] = bitmap[(size_t)(i + a) * nw + ((j + b) >> 5)];
+            }
             int nlit = 0;
+            unsigned refmask = 0;
 #pragma unroll
             for (int t = 0; t < NB; ++t) {
                 int a, b;
@@ -208,91 +253,120 @@ __global__ void __launch_bounds__(1024) median_solve_kernel(float* f, const unsi
                 unsigned short e = 0;
                 bool is_ref = false;
                 if (t < NC) {  // a causal cell may be an earlier candidate of this chunk
-                    const size_t wi = (size_t)y * nw + (x >> 5);
-                    const unsigned word = bitmap[wi];
-                    if ((word >> (x & 31)) & 1u) {
-                        const int k = wordoff[wi] + __popc(word & ((1u << (x & 31)) - 1u));
+                    if ((bw[t] >> (x & 31)) & 1u) {
+                        const int k = wordoff[(size_t)y * nw + (x >> 5)] + __popc(bw[t] & ((1u << (x & 31)) - 1u));
                         if (k >= base) {
                             e = (unsigned short)(0x8000u | (unsigned)(k - base));
                             is_ref = true;
+                            refmask |= 1u << t;
                         }
                     }
                 }
                 if (!is_ref) {  // final already (earlier chunks wrote their fills back before this chunk was built)
-                    const float v = f[(size_t)y * w + x];
-                    const bool ok = v <= vmax;
-                    e = ok ? (unsigned short)(int)v : MED_INVALID;
+                    const bool ok = fv[t] <= vmax;
+                    e = ok ? (unsigned short)(int)fv[t] : MED_INVALID;
                     nlit += ok ? 1 : 0;
                 }
-                win[(size_t)c * NB + t] = e;
+                win[(size_t)c * NBP + t] = e;
             }
+            win[(size_t)c * NBP + NB] = (unsigned short)refmask;  // the row's spare entry: which causal entries are references
             litv[c] = (unsigned char)nlit;
             val[c] = MED_UNRESOLVED;
         }
         __syncthreads();
+        MED_STAMP();
+        // Resolution without block barriers.  A warp takes one GROUP of 32 consecutive candidates at a time (groups wid,
+        // wid + nwarp, ...) and iterates on it until all 32 are resolved: a candidate whose references are all resolved takes
+        // its median, one that can no longer reach half a window of valid values is dropped early.  Dependencies mostly run
+        // between neighbouring candidates (the hole to the left, the holes one and two rows up), i.e. inside a group or into
+        // the groups just before it.  A reference always points to a LOWER index: the lowest unfinished group never waits
+        // for anybody, every warp of the block is resident, so this terminates.  val[] entries go unresolved -> final
+        // exactly once (one 16-bit store): whoever sees a final value sees the right one.
+        //
+        // Measured alternatives on the B200 (cycles of this phase, 1242x375: SGM frame with 1842 candidates / SAD block
+        // matching with 3065, see profiles/r02_median_solver.md): this form 177 k / 1.35 M; block-barrier rounds with one
+        // thread per candidate ~180 k / 3.4 M; per-lane instead of cooperative medians 294 k / 1.67 M; one candidate per
+        // warp, round-robin 158 k / 1.10 M; the same after peeling the never-fillable candidates to a fixpoint in parallel
+        // rounds (75 k / 116 k for the peeling) 145 k / 1.17 M; ONE warp walking the survivors in order 481 k / 1.76 M.
+        // They all end up near (number of filled holes) x (400 - 1000 cycles): consecutive holes are neighbours, so the
+        // medians form one long chain, and a median costs a dozen warp-wide votes / reductions at 20 - 40 cycles each.
         volatile unsigned short* vval = val;
-        for (;;) {
-            int open = 0;
-            for (int c = tid; c < cn; c += blockDim.x) {
-                if (vval[c] != MED_UNRESOLVED) continue;
-                const unsigned short* wc = win + (size_t)c * NB;
-                int unknown = 0, refvalid = 0;
-                unsigned short rv[NC];
-#pragma unroll
-                for (int t = 0; t < NC; ++t) {
-                    const unsigned short e = wc[t];
-                    unsigned short x = e;
-                    if (e & 0x8000u) {
-                        x = vval[e & 0x7fffu];
-                        unknown += x == MED_UNRESOLVED ? 1 : 0;
-                        refvalid += (x != MED_UNRESOLVED && x != MED_INVALID) ? 1 : 0;
-                    }
-                    rv[t] = x;
-                }
-                const int known = (int)litv[c] + refvalid;
-                if (unknown == 0) {
-                    unsigned short out = MED_INVALID;
-                    if (known > HALF) {
-                        // sorted[cnt / 2] = the smallest value with at least cnt / 2 + 1 window values <= it (bisection)
-                        int vals[NB];
-                        int lo = 0x7fff, hi = 0;
-#pragma unroll
-                        for (int t = 0; t < NB; ++t) {
-                            const int x = t < NC ? (int)rv[t] : (int)wc[t];
-                            vals[t] = x;  // invalid = 0x7fff sorts last
-                            if (x != MED_INVALID) {
-                                lo = min(lo, x);
-                                hi = max(hi, x);
-                            }
+        for (int g = wid; g * 32 < cn; g += nwarp) {
+            const int c = g * 32 + lane;
+            bool unresolved = c < cn;
+            const unsigned short* wc = win + (size_t)(unresolved ? c : 0) * NBP;
+            unsigned refmask = wc[NB];             // references still unresolved
+            int known = litv[unresolved ? c : 0];  // valid entries seen so far: literals + references resolved to a value
+            for (;;) {
+                bool ready = false, progress = false;
+                if (unresolved) {
+                    for (unsigned m = refmask; m; m &= m - 1) {
+                        const int t = __ffs(m) - 1;
+                        const unsigned short x = vval[wc[t] & 0x7fffu];
+                        if (x != MED_UNRESOLVED) {  // a resolved reference is looked at once
+                            refmask &= ~(1u << t);
+                            known += x != MED_INVALID ? 1 : 0;
+                            progress = true;
                         }
-                        const int need = known / 2 + 1;
-                        while (lo < hi) {
-                            const int mid = (lo + hi) >> 1;
-                            int le = 0;
-#pragma unroll
-                            for (int t = 0; t < NB; ++t) le += vals[t] <= mid ? 1 : 0;
-                            if (le >= need)
-                                hi = mid;
-                            else
-                                lo = mid + 1;
-                        }
-                        out = (unsigned short)lo;
                     }
-                    vval[c] = out;
-                } else if (known + unknown <= HALF) {
-                    vval[c] = MED_INVALID;  // can no longer reach half a window: resolved without waiting
-                } else {
-                    ++open;
+                    if (known + __popc(refmask) <= HALF) {  // can no longer reach half a window (or all known, too few): invalid
+                        vval[c] = MED_INVALID;
+                        unresolved = false;
+                        progress = true;
+                    } else {
+                        ready = refmask == 0;                // known > HALF: takes the median of its window
+                    }
                 }
+                // ready candidates are evaluated by the whole warp, one after the other: lane t holds window entry t, the
+                // median sorted[cnt / 2] = the smallest value with at least cnt / 2 + 1 entries <= it, by bisection on ballots
+                for (unsigned todo = __ballot_sync(FULL_MASK, ready); todo; todo &= todo - 1) {
+                    const int src = __ffs(todo) - 1, cs = g * 32 + src;
+                    int x = MED_INVALID;
+                    if (lane < NB) {
+                        x = win[(size_t)cs * NBP + lane];
+                        if (x & 0x8000) x = vval[x & 0x7fff];  // resolved: cs is ready
+                    }
+                    const bool ok = x != MED_INVALID;
+                    const int cnt = __popc(__ballot_sync(FULL_MASK, ok));
+                    int lo = __reduce_min_sync(FULL_MASK, x);              // invalid entries are 0x7fff: they sort last
+                    int hi = __reduce_max_sync(FULL_MASK, ok ? x : 0);
+                    const int need = cnt / 2 + 1;
+                    while (lo < hi) {
+                        const int mid = (lo + hi) >> 1;
+                        const int le = __popc(__ballot_sync(FULL_MASK, x <= mid));
+                        if (le >= need)
+                            hi = mid;
+                        else
+                            lo = mid + 1;
+                    }
+                    if (lane == src) {
+                        vval[cs] = (unsigned short)lo;
+                        unresolved = false;
+                    }
+                    progress = true;
+                }
+                __syncwarp();
+                if (__ballot_sync(FULL_MASK, unresolved) == 0) break;
+                // nothing moved: the group waits for an earlier group; leave the issue slots to the warps that can work
+                if (__ballot_sync(FULL_MASK, progress) == 0) __nanosleep(100);
             }
-            if (__syncthreads_count(open) == 0) break;
         }
+        __syncthreads();
         for (int c = tid; c < cn; c += blockDim.x) {
             const unsigned short v = val[c];
             if (v != MED_INVALID) f[list[base + c]] = (float)v;
         }
         __syncthreads();  // the fills are visible to the next chunk's window build
+        MED_STAMP();
     }
+#ifdef SGM_B200_TUNING
+    if (tid == 0) {
+        printf("median_solve: ncand %d, cycles since start:", ncand);
+        for (int k = 1; k < nstamp; ++k) printf(" %lld", tstamp[k] - tstamp[0]);
+        printf("  (1a rows, 1b scan, 1c list, build, resolve+writeback, ...)\n");
+    }
+#endif
+#undef MED_STAMP
 }
 
 // ---- speckle filter: exact 4-connected components under |a - b| < max_dis (src/Solver.cpp:514-566) -----
@@ -414,10 +488,10 @@ static void launch_lr_median_impl(const float* left, const float* right, float* 
     dim3 grid(nw, (h + LRC_TY - 1) / LRC_TY);
     lr_classify_kernel<WH, WW><<<grid, dim3(LRC_TX, LRC_TY), 0, st>>>(left, right, out_lr, out_med, bitmap, h, w, d, scale, thresh);
     lc.note("lr_classify_kernel");
-    constexpr size_t smem = (size_t)CHUNK * (MedianWin<WH, WW>::NB * 2 + 2 + 1);
+    constexpr size_t smem = (size_t)CHUNK * ((MedianWin<WH, WW>::NB + 2) * 2 + 2 + 1);
     auto kern = median_solve_kernel<WH, WW, CHUNK>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    kern<<<1, 1024, smem, st>>>(out_med, bitmap, wordoff, rowoff, scratch_b, h, w, d);
+    kern<<<1, 512, smem, st>>>(out_med, bitmap, wordoff, rowoff, scratch_b, h, w, d);
     lc.note("median_solve_kernel");
 }
 
