@@ -195,15 +195,18 @@ SGM_API int sgm_point_cloud(sgm_engine* e, const sgm_camera* cam, double* xyz, u
  * launches, and results come back in submission order.  No collective and no peer traffic: inputs and results cross PCIe.
  *
  *   sgm_stream_submit  copies the pair (and masks, nullable) into pinned staging and returns; it blocks only while the slot
- *                      the frame maps to is still occupied (back-pressure: at most n_devices * inflight frames are pending,
- *                      so a producer that never calls sgm_stream_next stalls there).  *frame_index (nullable) = k.
+ *                      the frame maps to is still occupied (back-pressure: at most n_devices * inflight frames occupy slots,
+ *                      so a producer whose consumer has stopped stalls there).  *frame_index (nullable) = k.
  *   sgm_stream_next    blocks until the OLDEST pending frame is done and hands out its final disparity (Solver::get_disp():
  *                      float32, (height/scale) x (width/scale), invalid = D+1): copied into dst when dst != NULL, and/or as
- *                      a pointer into the pinned result buffer (*view, dense rows) that stays valid until the next
- *                      sgm_stream_next / sgm_stream_destroy on this stream, or until n_devices * inflight further frames
- *                      have been submitted (the slot is then needed again).  Returns SGM_ERR_STATE when nothing is pending.
- * One producer thread and one consumer thread may call submit and next concurrently; two producers (or two consumers) may not.
- * A frame that fails reports its error from sgm_stream_next (message: sgm_stream_last_error) and the stream stays usable. */
+ *                      a pointer into the pinned result buffer (*view, dense rows).  A view keeps its slot occupied until
+ *                      sgm_stream_release or the next sgm_stream_next on this stream: it is never overwritten while it can
+ *                      still be read.  Returns SGM_ERR_STATE when no frame is pending (it never waits for a submit).
+ *   sgm_stream_pending frames that occupy a slot: submitted and not yet handed out, plus a view not yet released.  A caller
+ *                      that submits and collects on ONE thread calls sgm_stream_next whenever this equals
+ *                      n_devices * inflight, and so never waits for itself.
+ * One producer thread and one consumer thread may call submit and next / release concurrently; two producers (or two consumers)
+ * may not.  A frame that fails reports its error from sgm_stream_next (message: sgm_stream_last_error); the stream stays usable. */
 typedef struct sgm_stream sgm_stream; /* opaque */
 SGM_API int sgm_stream_create(sgm_stream** out, const sgm_params* params, const int* devices, int n_devices, int inflight);
 SGM_API void sgm_stream_destroy(sgm_stream* s);
@@ -211,7 +214,7 @@ SGM_API int sgm_stream_submit(sgm_stream* s, const uint8_t* left, size_t left_st
                               const uint8_t* sky_l, size_t sky_l_stride, const uint8_t* sky_r, size_t sky_r_stride,
                               uint64_t* frame_index);
 SGM_API int sgm_stream_next(sgm_stream* s, float* dst, size_t dst_stride, const float** view, uint64_t* frame_index);
-/* Frames submitted and not yet handed out by sgm_stream_next. */
+SGM_API int sgm_stream_release(sgm_stream* s);
 SGM_API int sgm_stream_pending(const sgm_stream* s);
 /* Kernel launches issued so far by all devices of the stream (bench.py's gpu_launches). */
 SGM_API uint64_t sgm_stream_launches(const sgm_stream* s);

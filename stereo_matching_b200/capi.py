@@ -28,7 +28,7 @@ EXPORTS = [
     "sgm_disparity_device", "sgm_tap_bytes", "sgm_get_tap", "sgm_get_size", "sgm_get_launch_count", "sgm_get_stage_ms",
     "sgm_get_stream", "sgm_device_bytes", "sgm_cost_volume_sad", "sgm_render_debug_view", "sgm_point_cloud",
     "sgm_get_subpixel_beta", "sgm_speckle_filter_static", "sgm_stream_create", "sgm_stream_destroy", "sgm_stream_submit",
-    "sgm_stream_next", "sgm_stream_pending", "sgm_stream_launches", "sgm_stream_last_error", "sgm_cost_volume_ssd", "sgm_cost_volume_ct",
+    "sgm_stream_next", "sgm_stream_release", "sgm_stream_pending", "sgm_stream_launches", "sgm_stream_last_error", "sgm_cost_volume_ssd", "sgm_cost_volume_ct",
 ]
 
 
@@ -97,6 +97,7 @@ def lib():
         L.sgm_stream_destroy.restype = None
         L.sgm_stream_submit.argtypes = [vp, vp, sz, vp, sz, vp, sz, vp, sz, C.POINTER(C.c_uint64)]
         L.sgm_stream_next.argtypes = [vp, vp, sz, C.POINTER(vp), C.POINTER(C.c_uint64)]
+        L.sgm_stream_release.argtypes = [vp]
         L.sgm_stream_pending.argtypes = [vp]
         L.sgm_stream_launches.argtypes = [vp]
         L.sgm_stream_launches.restype = C.c_uint64
@@ -326,11 +327,15 @@ class Stream:
         return self.next_into(out), out
 
     def next_view(self):
-        """(frame index, zero-copy float32 view of the pinned result); the view dies at the next next*() call."""
+        """(frame index, zero-copy float32 view of the pinned result); the view keeps its slot until release() or the next
+        next*() call."""
         k, ptr = C.c_uint64(), C.c_void_p()
         self._check(lib().sgm_stream_next(self._h, None, 0, C.byref(ptr), C.byref(k)))
         buf = (C.c_float * (self.img_h * self.img_w)).from_address(ptr.value)
         return k.value, np.frombuffer(buf, np.float32).reshape(self.img_h, self.img_w)
+
+    def release(self) -> None:
+        self._check(lib().sgm_stream_release(self._h))
 
     @property
     def pending(self) -> int:

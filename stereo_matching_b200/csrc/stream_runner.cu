@@ -9,7 +9,7 @@
 // Slot life cycle (one slot = one engine handle), every transition under the stream's mutex:
 //     FREE --submit: engine_stage (producer thread)--> STAGED --engine_launch_staged (device thread)--> LAUNCHED
 //          --sgm_stream_next: engine_wait_blocking (consumer thread)--> HELD (result pointer handed out)
-//          --the following sgm_stream_next--> FREE
+//          --sgm_stream_release / the following sgm_stream_next--> FREE
 // Frame k lives in slot (k / N) mod inflight of device k mod N, so both the producer and the consumer know where a frame
 // is without a queue, and results come out in submission order by construction.
 #include <cuda_runtime.h>
@@ -176,10 +176,8 @@ int sgm_stream_submit(sgm_stream* s, const uint8_t* left, size_t ls, const uint8
     const uint64_t k = s->submitted;
     DeviceLane* lane = nullptr;
     Slot& sl = slot_of(s, k, &lane);
-    // a result view handed out by sgm_stream_next also dies when a later submit needs its slot (otherwise a caller that
-    // submits and collects on one thread would wait for itself)
-    if (sl.state == SLOT_HELD) release_held(s);
-    // back-pressure: the slot still carries frame k - n_devices * inflight until the consumer has taken it
+    // back-pressure: the slot still carries frame k - n_devices * inflight until the consumer has taken it AND given a
+    // view of it back (sgm_stream_release, or its next sgm_stream_next): a result that is being read is never overwritten
     s->cv.wait(lock, [&] { return sl.state == SLOT_FREE; });
     lock.unlock();
     // the copy into pinned staging runs outside the lock: device threads and the consumer keep going
@@ -233,10 +231,17 @@ int sgm_stream_next(sgm_stream* s, float* dst, size_t dst_stride, const float** 
     return SGM_OK;
 }
 
+int sgm_stream_release(sgm_stream* s) {
+    if (!s) return SGM_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(s->mu);
+    release_held(s);
+    return SGM_OK;
+}
+
 int sgm_stream_pending(const sgm_stream* s) {
     if (!s) return -1;
     std::lock_guard<std::mutex> lock(const_cast<sgm_stream*>(s)->mu);
-    return (int)(s->submitted - s->delivered);
+    return (int)(s->submitted - s->delivered) + (s->holding ? 1 : 0);  // a held view still occupies its slot
 }
 
 uint64_t sgm_stream_launches(const sgm_stream* s) {

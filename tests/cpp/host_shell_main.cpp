@@ -4,13 +4,17 @@
 //
 //   host_shell_main <sgm|bm> H W SCALE D in_left.raw in_right.raw [sky_l.raw sky_r.raw|- -] out_prefix
 //   host_shell_main bench <sgm|bm> H W SCALE D in_left.raw in_right.raw FRAMES     (bench.py's `blocking` leg: one JSON line)
+//   host_shell_main stream H W SCALE D N_GPUS INFLIGHT FRAMES PAIR_DIR N_PAIRS     (BASELINE config 5: a frame stream over N GPUs
+//        from ONE process through the C runner sgm_stream_*; PAIR_DIR holds l<k>.raw / r<k>.raw; one JSON line on stderr)
 // TEST INFRASTRUCTURE.
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "inc/BM.h"
@@ -69,8 +73,87 @@ static int bench_main(int argc, char** argv) {
     return 0;
 }
 
+// FNV-1a 64 of a float image, the hash the golden vectors use.
+static unsigned long long fnv1a64(const void* data, size_t bytes) {
+    const unsigned char* p = static_cast<const unsigned char*>(data);
+    unsigned long long h = 1469598103934665603ull;
+    for (size_t k = 0; k < bytes; ++k) h = (h ^ p[k]) * 1099511628211ull;
+    return h;
+}
+
+// The reference's frame loop (node.cpp:49,93,104) over a stream of pairs and N GPUs: a producer thread submits, this thread
+// collects in order (zero-copy views of the pinned results), the first N_PAIRS results are hashed for the parity check.
+static int stream_main(int argc, char** argv) {
+    if (argc != 11) return 2;
+    const int h = std::atoi(argv[2]), w = std::atoi(argv[3]), s = std::atoi(argv[4]), d = std::atoi(argv[5]);
+    const int n_gpus = std::atoi(argv[6]), inflight = std::atoi(argv[7]), frames = std::atoi(argv[8]), n_pairs = std::atoi(argv[10]);
+    const std::string dir = argv[9];
+    if (n_gpus < 1 || inflight < 1 || frames < 1 || n_pairs < 1) return 2;
+    std::vector<Mat> L, R;
+    for (int k = 0; k < n_pairs; ++k) {
+        L.emplace_back(h, w, CV_8UC1);
+        R.emplace_back(h, w, CV_8UC1);
+        if (!read_raw((dir + "/l" + std::to_string(k) + ".raw").c_str(), L[k]) || !read_raw((dir + "/r" + std::to_string(k) + ".raw").c_str(), R[k])) return 3;
+    }
+    sgm_params p;
+    sgm_default_params(&p, h, w, s, d, SGM_ALGO_SGM);
+    sgm_stream* st = nullptr;
+    if (sgm_stream_create(&st, &p, nullptr, n_gpus, inflight) != SGM_OK) {
+        std::fprintf(stderr, "sgm_stream_create: %s\n", sgm_stream_last_error(nullptr));
+        return 4;
+    }
+    const int ih = h / s, iw = w / s;
+    uint64_t next_index = 0;  // frame indices are counted per stream, across the two runs below
+    auto run = [&](int count, std::vector<unsigned long long>* hashes) -> bool {
+        std::atomic<bool> ok(true), producing(true);
+        std::thread producer([&] {
+            for (int k = 0; k < count && ok; ++k)
+                if (sgm_stream_submit(st, L[k % n_pairs].ptr<uchar>(0), L[k % n_pairs].step, R[k % n_pairs].ptr<uchar>(0), R[k % n_pairs].step,
+                                      nullptr, 0, nullptr, 0, nullptr) != SGM_OK)
+                    ok = false;
+            producing = false;
+        });
+        int got = 0;
+        // collect until the producer is done and nothing is pending: also after a failure, so that a producer waiting for a
+        // slot is never left alone (it would wait for ever)
+        while (producing || sgm_stream_pending(st) > 0) {
+            if (sgm_stream_pending(st) == 0) {
+                std::this_thread::yield();  // the producer has not got there yet
+                continue;
+            }
+            const float* view = nullptr;
+            uint64_t idx = 0;
+            if (sgm_stream_next(st, nullptr, 0, &view, &idx) != SGM_OK || idx != next_index) ok = false;
+            ++next_index;
+            if (ok && hashes && got < n_pairs) hashes->push_back(fnv1a64(view, (size_t)ih * iw * sizeof(float)));
+            sgm_stream_release(st);  // done with the view: its slot may take a new frame
+            ++got;
+        }
+        producer.join();
+        return ok && got == count;
+    };
+    std::vector<unsigned long long> hashes;
+    if (!run(std::max(n_pairs, 4 * n_gpus * inflight), &hashes)) {  // warm-up + parity frames
+        std::fprintf(stderr, "stream failed: %s\n", sgm_stream_last_error(st));
+        return 5;
+    }
+    const double t0 = get_cur_ms();
+    if (!run(frames, nullptr)) {
+        std::fprintf(stderr, "stream failed: %s\n", sgm_stream_last_error(st));
+        return 5;
+    }
+    const double ms = get_cur_ms() - t0;
+    std::fprintf(stderr, "{\"frames\": %d, \"n_gpus\": %d, \"inflight\": %d, \"wall_ms\": %.2f, \"frames_per_s\": %.2f, \"launches\": %llu, \"first_hashes\": [",
+                 frames, n_gpus, inflight, ms, 1e3 * frames / ms, (unsigned long long)sgm_stream_launches(st));
+    for (size_t k = 0; k < hashes.size(); ++k) std::fprintf(stderr, "%s\"%016llx\"", k ? ", " : "", hashes[k]);
+    std::fprintf(stderr, "]}\n");
+    sgm_stream_destroy(st);
+    return 0;
+}
+
 int main(int argc, char** argv) {
     if (argc >= 2 && std::strcmp(argv[1], "bench") == 0) return bench_main(argc, argv);
+    if (argc >= 2 && std::strcmp(argv[1], "stream") == 0) return stream_main(argc, argv);
     if (argc != 11) {
         std::fprintf(stderr, "usage: %s <sgm|bm> H W SCALE D left.raw right.raw sky_l.raw|- sky_r.raw|- out_prefix\n", argv[0]);
         return 2;

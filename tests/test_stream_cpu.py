@@ -9,6 +9,8 @@ import pytest
 
 from stereo_matching_b200 import stream
 
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
 
 class FakeEngine:
     """Stand-in for a capi.SGM handle: 'disparity' = a checksum image of the inputs, available only after wait()."""
@@ -111,3 +113,18 @@ def test_two_ranks_gloo_cover_the_stream_exactly_once():
     assert len(merged) == n and [len(g) for g in gathered] == stream.shard_sizes(n, 2)
     for k, d in merged:
         assert np.array_equal(np.asarray(d, np.float32), _expected(k))
+
+
+def test_c_stream_runner_host_logic_against_mock_engine(tmp_path):
+    """The C frame-stream runner (stereo_matching_b200/csrc/stream_runner.cu: slots, back-pressure, in-order delivery, held views,
+    device lanes, failing frames) compiled as plain C++ against a MOCK engine (tests/cpp/stream_runner_mock.cpp): the N>1 host
+    logic without a GPU, with a producer and a consumer thread and with one thread alone."""
+    import subprocess
+
+    exe = str(tmp_path / "stream_mock")
+    env = {k: v for k, v in os.environ.items() if k not in ("CXX", "CC")}
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-pthread", "-I/usr/local/cuda/include", "-I" + os.path.join(ROOT, "include"), "-x", "c++",
+                           os.path.join(ROOT, "stereo_matching_b200", "csrc", "stream_runner.cu"),
+                           os.path.join(ROOT, "tests", "cpp", "stream_runner_mock.cpp"), "-o", exe], env=env)
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and "all checks passed" in out.stdout, out.stdout + out.stderr

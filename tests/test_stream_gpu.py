@@ -80,10 +80,15 @@ def test_stream_zero_copy_view_and_masks():
     assert k0 == 0 and bits_equal(np.array(v0), want_sky)
     k1, v1 = st.next_view()                  # v0 is dead from here on
     assert k1 == 1 and bits_equal(np.array(v1), want)
-    # a held view is released when a later submit needs its slot: no self-deadlock on one thread
-    st.submit(L, R)
-    st.submit(L, R)
-    assert st.next()[0] == 2 and st.next()[0] == 3
+    # a held view occupies its slot: it counts as pending (so a one-thread caller collects before it would wait for itself)
+    # until it is released
+    assert st.pending == 1
+    st.submit(L, R)                          # frame 2 -> the other slot
+    assert st.pending == st.capacity == 2
+    st.release()
+    assert st.pending == 1
+    st.submit(L, R)                          # frame 3 -> the slot that was held
+    assert st.next()[0] == 2 and st.next()[0] == 3 and st.pending == 0
     st.close()
 
 
@@ -105,3 +110,22 @@ def test_stream_other_algorithms_and_bad_arguments():
         capi.Stream(h, w, 1, 48, devices=(0,), inflight=1)      # sgm_create's own validation comes through
     with pytest.raises(capi.SgmError):
         capi.Stream(h, w, 1, d, devices=(99,), inflight=1)
+
+
+def test_cpp_stream_driver_matches_golden_and_uses_every_gpu():
+    # BASELINE.json configs[4] in miniature: the C++ driver's `stream` mode (one process, producer + consumer threads,
+    # sgm_stream over every GPU of the box) must return the reference's golden results for the bench pairs, in order
+    import json
+    import os
+    import subprocess
+    import sys
+
+    torch = pytest.importorskip("torch")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.check_call(["make", "-s", "-C", os.path.join(root, "stereo_matching_b200", "host"), "_build/host_shell_main"],
+                          env={k: v for k, v in os.environ.items() if k not in ("CXX", "CC")})
+    n = min(torch.cuda.device_count(), 8)
+    out = subprocess.run([sys.executable, os.path.join(root, "tests", "stream_config4.py"), str(n), "96", "3"], capture_output=True, text=True, timeout=150)
+    assert out.returncode == 0, out.stdout + out.stderr
+    j = json.loads(out.stdout.strip().splitlines()[-1])
+    assert j["parity_first_8"] and j["n_gpus"] == n and j["frames"] == 96 and j["launches"] > 96 * 15
