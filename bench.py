@@ -381,7 +381,11 @@ def run_gpu_arm(args, rank, world, local, dist):
     wall_e2e = (time.perf_counter() - wall0) * 1e3
     ms_e2e = max_over_ranks(dist, torch, e0.elapsed_time(e1), device)
     launches_e2e = runner.launches - launches0
-    parity = check_first_results(first8) if rank == 0 else None
+    # the golden vectors are the reference's (float32, recursive cost filter): they apply to the headline mode only; the
+    # secondary modes switch the cost filter off and have their own goldens in tests/ (kat_hashes_integer.json)
+    parity = None
+    if rank == 0:
+        parity = check_first_results(first8) if args.mode == "reference" else {"frames_checked": 0, "ok": None, "note": "secondary mode: checked in tests/test_parity_gpu.py"}
 
     # ---- roofline: aggregation stage timed alone on its launching stream (serial frames, engine-side CUDA events) ----
     stage_sum = {}

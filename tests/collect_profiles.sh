@@ -7,13 +7,13 @@ mode=${2:-reference}
 what=${3:-all}
 out=gpurun_out
 mkdir -p $out
-python bench.py --mode $mode --no-cpu-baseline $BENCH_EXTRA > $out/r02_${tag}_bench_line.json 2> $out/r02_${tag}_bench.err || exit 1
-python tests/perf_configs.py --frames 60 > $out/r02_${tag}_perf_configs.jsonl 2>> $out/r02_${tag}_bench.err
+python bench.py --mode $mode --no-cpu-baseline --no-configs $BENCH_EXTRA > $out/r02_${tag}_bench_line.json 2> $out/r02_${tag}_bench.err || exit 1
+
 [ "$what" = noncu ] && exit 0
 # launch list of one bench step (serialised, cold cache: shares only)
 ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 40 --csv --log-file $out/r02_${tag}_launches_bench_kitti128.csv \
-    python bench.py --mode $mode --steps 1 --no-cpu-baseline > $out/ncu_launch.log 2>&1
+    python bench.py --mode $mode --steps 1 --no-cpu-baseline --no-configs > $out/ncu_launch.log 2>&1
 # full capture of the cost / aggregation kernels of one warm frame
 ncu --set full --clock-control none --import-source on -k regex:"sgm_sweep|hpair|vfilter|hfilter|hamming" -s 15 -c 5 -o $out/r02_${tag}_agg \
-    python bench.py --mode $mode --steps 1 --no-cpu-baseline > $out/ncu_full.log 2>&1
+    python bench.py --mode $mode --steps 1 --no-cpu-baseline --no-configs > $out/ncu_full.log 2>&1
 tail -2 $out/ncu_full.log
