@@ -20,6 +20,13 @@
 
 #include "sgm_b200.h"
 
+#if defined(__has_include)
+#if __has_include("../LKRefine/LKSubPixel.h")
+#include "../LKRefine/LKSubPixel.h"  // the package's own sub-pixel refiner (inc/Solver.h:7); never invoked on the path (src/SGM.cpp:823-824)
+#define SGM_B200_HAVE_LKREFINE 1
+#endif
+#endif
+
 // Matching parameters.  Names and values are the reference's (inc/Solver.h:10-20); they are handed to the engine through
 // sgm_params, so editing them here changes the device pipeline exactly like editing them changed the CPU one.
 const int WIN_H = 7;              // census window, rows
@@ -71,6 +78,18 @@ protected:
     Mat colored_disp;               // CV_8UC3 scratch of show_disp()
     Mat sky_mask, sky_mask_beta;    // masks handed to the last 4-argument process() (kept between frames like the reference)
 
+    // Host MIRRORS of device state, under the reference's names (inc/Solver.h:47-49).  The reference computes into these
+    // arrays on the CPU; here the volumes live in device memory and these stay NULL until one of the build_* / fetch_*
+    // helpers below is called, which copies what the device computed for the LAST frame (sgm_get_tap).  Nothing on the
+    // path reads them.
+    uint64_t *cost_table_l, *cost_table_r;  // census tables [img_h * img_w]
+    float *cost;                            // cost volume [img_h * img_w * max_disp] (allocated on first use: 4 * W * H * D bytes)
+    float *weight;                          // window weights; WEIGHTED_COST is 0 in the reference and here: always NULL
+
+#ifdef SGM_B200_HAVE_LKREFINE
+    LKSubPixelPtr lkptr;                    // created like the reference does (src/Solver.cpp:51), never invoked
+#endif
+
     sgm_engine *engine;             // the device pipeline (NULL until a derived constructor called open_engine)
     bool two_views;                 // the pipeline also computes the right ("beta") view (SGM; BM is left-only)
 
@@ -79,6 +98,21 @@ protected:
     void open_engine(int algo, int paths, int full_h, int full_w);
     // Runs one frame on the device and refreshes disp / disp_beta / filtered_disp / filtered_disp_beta.
     void run_engine(Mat &l, Mat &r);
+
+    // The reference's protected stage helpers (inc/Solver.h:55-69), kept by name.  In the reference a subclass calls them in
+    // sequence to BUILD the result on the CPU; here process() has already run every stage on the device, so they REFRESH the
+    // mirrors above from the last frame instead (and the in-place filters have nothing left to do):
+    void build_cost_table();            // cost_table_l / cost_table_r <- census tables of the last frame
+    void build_dsi();                   // cost <- the (filtered) cost volume of the left view
+    void build_dsi_from_table();        //   "
+    void build_dsi_from_table_beta();   // cost <- the cost volume of the right view (SGM only)
+    void cost_horizontal_filter(int win_size);  // no-op: the volume fetched above is already filtered (fused on the device)
+    void cost_vertical_filter(int win_size);    // no-op
+    float find_dsi_mean_max();          // prints max and mean of the `cost` mirror, returns the mean (src/Solver.cpp:251-270)
+    float find_table_mean_max();        // the same over the cost_table_r mirror, divided like the reference does (:273-293)
+    void fetch_cost(float *p);          // src/Solver.cpp:371-374: copies an external volume into `cost`
+    void compute_subpixel(const Mat &disp, Mat &filtered_disp);  // filtered_disp <- the device's sub-pixel image for `disp` (left or beta)
+    void post_filter();                 // no-op: median and speckle filter ran on the device; filtered_disp holds their result
     // Hooks the reference offered for copying externally computed results into the Mats (src/Solver.cpp:376-400).
     void fetch_disparity(uchar *d);
     void fetch_disparity(float *d);

@@ -7,6 +7,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 namespace {
@@ -22,7 +23,8 @@ void die(const char *what, const sgm_engine *e)
 }  // namespace
 
 Solver::Solver(int h, int w, int s, int d)
-    : img_h(0), img_w(0), scale(s), max_disp(d), invalid_disp(d + 1), engine(nullptr), two_views(false)
+    : img_h(0), img_w(0), scale(s), max_disp(d), invalid_disp(d + 1), cost_table_l(nullptr), cost_table_r(nullptr), cost(nullptr),
+      weight(nullptr), engine(nullptr), two_views(false)
 {
     // same domain as the reference (src/Solver.cpp:6-10); d == 256 is the engine's widened mode (uint16 disparities
     // inside, the CV_8UC1 `disp` Mats then saturate, get_disp() stays exact)
@@ -37,11 +39,17 @@ Solver::Solver(int h, int w, int s, int d)
     filtered_disp.create(img_h, img_w, CV_32FC1);
     filtered_disp_beta.create(img_h, img_w, CV_32FC1);
     colored_disp.create(img_h, img_w, CV_8UC3);
+#ifdef SGM_B200_HAVE_LKREFINE
+    lkptr = LKSubPixel::create(h, w, s, d);  // src/Solver.cpp:51; the refinement itself is never invoked (src/SGM.cpp:823-824)
+#endif
 }
 
 Solver::~Solver()
 {
     sgm_destroy(engine);
+    delete[] cost_table_l;
+    delete[] cost_table_r;
+    delete[] cost;
 }
 
 void Solver::open_engine(int algo, int paths, int full_h, int full_w)
@@ -111,6 +119,75 @@ void Solver::run_engine(Mat &l, Mat &r)
         if (sgm_get_subpixel_beta(engine, filtered_disp_beta.ptr<float>(0), filtered_disp_beta.step) != SGM_OK) die("filtered_disp_beta", engine);
     }
     // the masks stay set until the next 4-argument process(), as in the reference (src/SGM.cpp:831-833)
+}
+
+// ---- the reference's protected stage helpers as refreshers of the host mirrors (see inc/Solver.h) -------------------------
+void Solver::build_cost_table()
+{
+    const size_t n = (size_t)img_h * img_w;
+    if (!cost_table_l) cost_table_l = new uint64_t[n];
+    if (!cost_table_r) cost_table_r = new uint64_t[n];
+    if (sgm_get_tap(engine, SGM_TAP_CENSUS, 0, cost_table_l, n * sizeof(uint64_t)) != SGM_OK) die("build_cost_table", engine);
+    if (sgm_get_tap(engine, SGM_TAP_CENSUS, 1, cost_table_r, n * sizeof(uint64_t)) != SGM_OK) die("build_cost_table", engine);
+}
+
+static void fetch_volume(sgm_engine *engine, float *&cost, int view, size_t count)
+{
+    if (!cost) cost = new float[count];
+    if (sgm_get_tap(engine, SGM_TAP_COST, view, cost, count * sizeof(float)) != SGM_OK) die("build_dsi", engine);
+}
+
+void Solver::build_dsi() { fetch_volume(engine, cost, 0, (size_t)img_h * img_w * max_disp); }
+void Solver::build_dsi_from_table() { fetch_volume(engine, cost, 0, (size_t)img_h * img_w * max_disp); }
+void Solver::build_dsi_from_table_beta() { fetch_volume(engine, cost, 1, (size_t)img_h * img_w * max_disp); }
+void Solver::cost_horizontal_filter(int) {}  // fused into the volume kernel on the device (src/Solver.cpp:296-330)
+void Solver::cost_vertical_filter(int) {}    // done on the device (src/Solver.cpp:333-368)
+void Solver::post_filter() {}                // done on the device (src/Solver.cpp:600-635); filtered_disp holds the result
+
+float Solver::find_dsi_mean_max()
+{
+    if (!cost) build_dsi();
+    double max_cost = 0, mean_cost = 0;
+    const size_t count = (size_t)img_h * img_w * max_disp;
+    for (size_t k = 0; k < count; ++k) {
+        mean_cost += cost[k];
+        if (cost[k] > max_cost) max_cost = cost[k];
+    }
+    mean_cost /= (double)count;
+    std::printf("max_cost: %lf, mean_cost: %lf\n", max_cost, mean_cost);
+    return (float)mean_cost;
+}
+
+float Solver::find_table_mean_max()
+{
+    if (!cost_table_r) build_cost_table();
+    double max_cost = 0, mean_cost = 0;
+    const size_t n = (size_t)img_h * img_w;
+    for (size_t k = 0; k < n; ++k) {
+        mean_cost += (double)cost_table_r[k];
+        if ((double)cost_table_r[k] > max_cost) max_cost = (double)cost_table_r[k];
+    }
+    mean_cost /= (double)(n * max_disp);  // the reference divides by h * w * max_disp here too (src/Solver.cpp:290)
+    std::printf("max_cost: %lf, mean_cost: %lf\n", max_cost, mean_cost);
+    return (float)mean_cost;
+}
+
+void Solver::fetch_cost(float *p)
+{
+    const size_t count = (size_t)img_h * img_w * max_disp;
+    if (!cost) cost = new float[count];
+    std::memcpy(cost, p, count * sizeof(float));  // src/Solver.cpp:371-374
+}
+
+// src/Solver.cpp:569-597 runs inside the device pipeline; this returns its result for the disparity image given: the left
+// view's for `disp`, the right view's for `disp_beta` (any other Mat: the left view's).
+void Solver::compute_subpixel(const Mat &d, Mat &out)
+{
+    const int view = (two_views && &d == &disp_beta) ? 1 : 0;
+    if (out.rows != img_h || out.cols != img_w || out.type() != CV_32FC1) out.create(img_h, img_w, CV_32FC1);
+    std::vector<float> tmp((size_t)img_h * img_w);
+    if (sgm_get_tap(engine, SGM_TAP_SUBPIXEL, view, tmp.data(), tmp.size() * sizeof(float)) != SGM_OK) die("compute_subpixel", engine);
+    for (int i = 0; i < img_h; ++i) std::memcpy(out.ptr<float>(i), tmp.data() + (size_t)i * img_w, (size_t)img_w * sizeof(float));
 }
 
 void Solver::fetch_disparity(uchar *d)

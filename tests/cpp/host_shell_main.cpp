@@ -40,6 +40,38 @@ static void write_raw(const std::string& path, const Mat& m, size_t elem) {
     std::fclose(f);
 }
 
+// The protected surface of inc/Solver.h:38-69, reached the way a subclass of the reference would reach it.
+struct ProbeSGM : public SGM {
+    ProbeSGM(int h, int w, int s, int d) : SGM(h, w, s, d) {}
+    // census tables, the filtered left / right cost volumes and the sub-pixel images of the last frame, through the helpers
+    bool dump(const std::string& out) {
+        build_cost_table();
+        build_dsi_from_table();
+        cost_horizontal_filter(COST_WIN_W / scale);
+        cost_vertical_filter(COST_WIN_H / scale);
+        const size_t n = (size_t)img_h * img_w, N = n * max_disp;
+        FILE* f = std::fopen((out + "_ctl.u64").c_str(), "wb");
+        std::fwrite(cost_table_l, sizeof(uint64_t), n, f);
+        std::fclose(f);
+        f = std::fopen((out + "_cost_l.f32").c_str(), "wb");
+        std::fwrite(cost, sizeof(float), N, f);
+        std::fclose(f);
+        const float mean_l = find_dsi_mean_max();
+        build_dsi_from_table_beta();
+        f = std::fopen((out + "_cost_r.f32").c_str(), "wb");
+        std::fwrite(cost, sizeof(float), N, f);
+        std::fclose(f);
+        Mat sub_r;
+        compute_subpixel(disp_beta, sub_r);
+        write_raw(out + "_sub_r.f32", sub_r, sizeof(float));
+        write_raw(out + "_disp8.u8", disp, 1);
+        write_raw(out + "_fbeta.f32", filtered_disp_beta, sizeof(float));
+        post_filter();
+        std::printf("probe mean_l %f weight %p\n", mean_l, (void*)weight);
+        return weight == nullptr && cost != nullptr;
+    }
+};
+
 // Blocking frame loop exactly as node.cpp:93,104 runs it: process(l, r) then get_disp(), one frame at a time.
 static int bench_main(int argc, char** argv) {
     if (argc != 10) return 2;
@@ -174,10 +206,11 @@ int main(int argc, char** argv) {
     const std::string out = argv[10];
 
     SolverPtr sv;
+    std::shared_ptr<ProbeSGM> probe;
     if (bm)
         sv = std::make_shared<BM>(h, w, s, d);
     else
-        sv = std::make_shared<SGM>(h, w, s, d);
+        sv = probe = std::make_shared<ProbeSGM>(h, w, s, d);
     const double t0 = get_cur_ms();
     if (have_sky)
         sv->process(img_l, img_r, sky_l, sky_r);
@@ -192,6 +225,7 @@ int main(int argc, char** argv) {
                 debug_view.cols, debug_view.channels());
     write_raw(out + "_disp.f32", disp, sizeof(float));
     write_raw(out + "_debug.bgr", debug_view, 3);
+    if (probe && !probe->dump(out)) return 6;
     // second frame on the same solver (node.cpp would loop over frames): must give the same result
     if (have_sky)
         sv->process(img_l, img_r, sky_l, sky_r);

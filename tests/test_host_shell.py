@@ -75,7 +75,7 @@ def test_division_by_window_size_is_exact():
     assert out.returncode == 0, out.stdout
 
 
-def _run_driver(tmp, algo, h, w, s, d, L, R, sky, env=None):
+def _run_driver(tmp, algo, h, w, s, d, L, R, sky, env=None, want_probe=None):
     exe = _make("_build/host_shell_main")
     L.tofile(os.path.join(tmp, "l.raw"))
     R.tofile(os.path.join(tmp, "r.raw"))
@@ -93,6 +93,14 @@ def _run_driver(tmp, algo, h, w, s, d, L, R, sky, env=None):
     disp2 = np.fromfile(prefix + "_disp2.f32", np.float32).reshape(ih, iw)
     dbg = np.fromfile(prefix + "_debug.bgr", np.uint8).reshape(2 * ih, iw, 3)
     cloud = np.fromfile(prefix + "_cloud.f64", np.float64).reshape(-1, 3)
+    if algo == "sgm" and want_probe is not None:  # the protected surface, dumped by a subclass (ProbeSGM in the driver)
+        want_probe.update(
+            ctl=np.fromfile(prefix + "_ctl.u64", np.uint64).reshape(ih, iw),
+            cost_l=np.fromfile(prefix + "_cost_l.f32", np.float32).reshape(ih, iw, d),
+            cost_r=np.fromfile(prefix + "_cost_r.f32", np.float32).reshape(ih, iw, d),
+            sub_r=np.fromfile(prefix + "_sub_r.f32", np.float32).reshape(ih, iw),
+            disp8=np.fromfile(prefix + "_disp8.u8", np.uint8).reshape(ih, iw),
+            fbeta=np.fromfile(prefix + "_fbeta.f32", np.float32).reshape(ih, iw))
     return disp, disp2, dbg, cloud, r.stdout
 
 
@@ -124,9 +132,18 @@ def _colormap(f, d):
 def test_node_style_driver_matches_oracle(algo, h, w, s, d, sky):
     L, R, _ = synth.random_dot_pair(h, w, seed=h + d, bg=5, fg=min(17, d // 2), noise=15)
     masks = synth.sky_masks(h // s, w // s) if sky else None
-    want = restate.process(L, R, s, d, algo, *(masks or (None, None)))["f_final"]
+    taps = restate.process(L, R, s, d, algo, *(masks or (None, None)), taps=restate.ALL_TAPS)
+    want = taps["f_final"]
+    probe = {}
     with tempfile.TemporaryDirectory() as tmp:
-        disp, disp2, dbg, cloud, log = _run_driver(tmp, algo, h, w, s, d, L, R, masks)
+        disp, disp2, dbg, cloud, log = _run_driver(tmp, algo, h, w, s, d, L, R, masks, want_probe=probe)
+    if algo == "sgm":
+        # the protected members of inc/Solver.h:43-69 as a subclass sees them: census table, filtered cost volumes of both views
+        # (build_dsi_from_table / _beta), compute_subpixel(disp_beta), the CV_8UC1 disp and filtered_disp_beta
+        assert bits_equal(probe["ctl"], taps["census"][0])
+        assert bits_equal(probe["cost_l"], taps["cost_hv"][0]) and bits_equal(probe["cost_r"], taps["cost_hv"][1])
+        assert bits_equal(probe["sub_r"], taps["fsub"][1]) and bits_equal(probe["fbeta"], taps["fsub"][1])
+        assert np.array_equal(probe["disp8"], np.minimum(taps["disp"][0], 255).astype(np.uint8))
     assert bits_equal(disp, want), "get_disp() of the C++ shell differs from the oracle"
     assert bits_equal(disp2, want), "second frame on the same solver differs"
     assert "time cost" in log

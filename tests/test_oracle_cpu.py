@@ -235,3 +235,42 @@ def test_point_cloud_restatement_basics():
     assert xyz.shape == (2, 3) and list(inten) == [left[1, 2], left[3, 0]]
     z0 = (np.float64(np.float32(700.0) + np.float32(720.0)) / 2.0) * 0.5 / (np.float64(np.float32(10.0)) + 1e-6)
     assert xyz[0, 2] == z0 and xyz[0, 0] == np.float64(np.float32(2 - 3.0)) * z0 / np.float64(np.float32(700.0))
+
+
+NODE_REF = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "node_ref")
+
+
+@pytest.mark.skipif(not os.path.exists(NODE_REF), reason="oracle/_ref/node_ref (the reference's node.cpp, linked) not built")
+@pytest.mark.parametrize("h,w,d,scale,sky_rows,noise", [(120, 200, 64, 1, 0, 15), (150, 260, 64, 2, 20, 10), (96, 192, 128, 1, 24, 30)])
+def test_point_cloud_restatement_against_reference_node_cpp(tmp_path, h, w, d, scale, sky_rows, noise):
+    # N3 pin: the disparity -> point cloud loop exists only inside main() of the reference's node.cpp (:119-143).  The
+    # UNMODIFIED node.cpp is linked with the reference's own solver and I/O stubs (oracle/node_harness.cpp), fed a synthetic
+    # pair, and its stereo_pts / stereo_pixel vectors are compared with restate.point_cloud — the checker of the GPU tests
+    # (tests/test_host_shell.py, tests/test_views_gpu.py) — bit for bit.
+    import subprocess
+
+    L, R, _ = synth.random_dot_pair(h, w, seed=h + d, bg=5, fg=min(17, d // 2), noise=noise)
+    L.tofile(tmp_path / "l.raw")
+    R.tofile(tmp_path / "r.raw")
+    env = dict(os.environ, NODE_LEFT_RAW=str(tmp_path / "l.raw"), NODE_RIGHT_RAW=str(tmp_path / "r.raw"), NODE_OUT=str(tmp_path / "out"),
+               NODE_SKY_ROWS=str(sky_rows), ROS_PARAM__sgm_node_img_h=str(h), ROS_PARAM__sgm_node_img_w=str(w),
+               ROS_PARAM__sgm_node_scale=str(scale), ROS_PARAM__sgm_node_max_disp=str(d), OMP_NUM_THREADS="1")
+    r = subprocess.run([NODE_REF], env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-500:] + r.stderr[-500:]
+    ih, iw = h // scale, w // scale
+    disp = np.fromfile(tmp_path / "out_disp.f32", np.float32).reshape(ih, iw)
+    xyz = np.fromfile(tmp_path / "out_xyz.f64", np.float64).reshape(-1, 3)
+    inten = np.fromfile(tmp_path / "out_int.u8", np.uint8)
+    # the disparity node.cpp published is the reference solver's (same sources as oracle/_ref/libsgm_ref.so) ...
+    sl = sr = None
+    if sky_rows:
+        sl = np.zeros((ih, iw), np.uint8)
+        sl[:sky_rows] = 255
+        sr = sl.copy()
+    refbind.set_threads(1)
+    assert bits_equal(disp, refbind.process("sgm", L, R, scale, d, sl, sr)["fdisp"])
+    # ... and its point cloud is what the restatement computes from that disparity
+    want_xyz, want_int = restate.point_cloud(disp, L, d, scale, 718.856, 718.856, 607.1928, 185.2157, 0.5, 100.0)
+    assert f"pointcloud size: {len(want_int)}, {len(want_int)}" in r.stdout
+    assert xyz.shape == want_xyz.shape and np.array_equal(xyz.view(np.uint64), want_xyz.view(np.uint64))
+    assert np.array_equal(inten, want_int) and len(inten) > 50   # (scale 2 halves the disparities: most points pass the 100 m range cut)
