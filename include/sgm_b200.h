@@ -71,11 +71,13 @@ typedef struct sgm_params {
 
 #define SGM_FLAG_KEEP_VOLUMES 0x1u /* keep the summed path volume S of both views readable through sgm_get_tap (debug; costs 4 B per disp.px) */
 #define SGM_FLAG_LINE_WALKERS 0x4u /* aggregate with the independent line-walker kernels (8 launches, 88 B/disp.px) instead of the fused sweeps */
-/* Integer / DPX mode (north_star): with the cost filter switched off (box_w / scale == box_h / scale == 1) and no
- * sky mask every number on the reference's path (src/SGM.cpp:82-418) is an integer < 2^15 that float32 holds exactly, so the
- * engine keeps the volumes as 16-bit integers (half the bytes) and runs the min-plus recurrences on s16x2 pairs with the DPX
- * instructions VIMNMX3 / VIADDMNMX.  Results are IDENTICAL to the float path under the same parameters (tested tap by tap);
- * sgm_create rejects parameter sets for which that would not hold (SGM_ERR_UNSUPPORTED). */
+/* Integer / DPX mode (north_star): with the cost filter switched off (box_w / scale == box_h / scale == 1) every
+ * number on the reference's path (src/SGM.cpp:82-418) is an integer < 2^15 that float32 holds exactly, so the engine keeps the
+ * volumes as 16-bit integers (half the bytes) and runs the min-plus recurrences on s16x2 pairs with the DPX instructions
+ * VIMNMX3 / VIADDMNMX.  Results are IDENTICAL to the float path under the same parameters (tested tap by tap); sgm_create rejects
+ * parameter sets for which that would not hold (SGM_ERR_UNSUPPORTED).  Sky masks are accepted (P2 <= 1365): masked pixels cost
+ * 2 * P2 instead of the reference's 999999 (src/Solver.cpp:165-179), which provably changes no disparity, sub-pixel value or
+ * validity anywhere; only the cost / path-sum debug taps of the masked pixels themselves read 2 * P2 + t instead of 999999 + t. */
 #define SGM_FLAG_INTEGER 0x8u
 /* The C++ shells keep Solver's protected result Mats (disp, disp_beta, filtered_disp_beta: inc/Solver.h:43-46) filled after every
  * process(): with this flag the 8-bit disparities of both views (narrowed on the device) and the right view's sub-pixel image are

@@ -576,10 +576,21 @@ void launch_hamming_hfilter(const uint64_t* ct_l, const uint64_t* ct_r, const ui
 // s16x2 words, two disparities {2k, 2k+1} per 32-bit word, the layout S16x2Arith works on.  Block = (row, view); both
 // census rows are staged in shared memory like hamming_hfilter_row_kernel does; a thread produces two adjacent words
 // (four disparities) per step and stores them as one 8-byte access, fully coalesced along d.
+//
+// Sky masks (src/Solver.cpp:165-179: masked pixels cost 0 at d = 0 and 999999 elsewhere): 999999 does not fit 16 bits, so masked
+// pixels get sky_big = 2 * P2 instead, which provably gives the same results.  With the cost filter off a masked pixel's path
+// values are L(0) <= P2 and L(d > 0) = fill + t, t in [0, P2]; every later min(L(d), L(d +- 1) + P1, m + P2) with m = L(0)
+// takes m + P2 (or L(0) + P1 at d = 1) whether the fill is 999999 or any value >= 2 * P2, so the path values of all other
+// pixels are unchanged; at the masked pixel itself S(0) <= 8 * P2 < 8 * fill <= S(d > 0), so the winner is d = 0 and
+// S(0) / S(second) <= 0.5 < UNIQUE_RATIO keeps it valid, as in the reference.  Only the cost / path-sum TAPS of masked pixels
+// differ from the float volumes (fill + t instead of 999999 + t).
 __global__ void __launch_bounds__(256) hamming_s16x2_kernel(const uint64_t* __restrict__ ct_l, const uint64_t* __restrict__ ct_r,
-                                                            uint2* __restrict__ cost, int h, int w, int d, int scale) {
+                                                            const uint8_t* __restrict__ sky_l, const uint8_t* __restrict__ sky_r,
+                                                            unsigned sky_big, uint2* __restrict__ cost, int h, int w, int d, int scale) {
     extern __shared__ __align__(16) unsigned char hsm[];
     const int i = blockIdx.x, view = blockIdx.y;
+    const uint8_t* sky = view == 0 ? sky_l : sky_r;
+    if (sky) sky += (size_t)i * w;
     uint64_t* rowA = reinterpret_cast<uint64_t*>(hsm);
     uint64_t* rowB = rowA + w;  // view 0: right row padded on the left by d entries; view 1: left row padded on the right
     const uint64_t* srcA = (view == 0 ? ct_l : ct_r) + (size_t)i * w;
@@ -591,9 +602,11 @@ __global__ void __launch_bounds__(256) hamming_s16x2_kernel(const uint64_t* __re
     const int g = threadIdx.x & (q - 1);      // this thread's group of four disparities 4g .. 4g+3
     const int p = threadIdx.x / q, np = blockDim.x / q;
     uint2* out = cost + ((size_t)view * h + i) * (size_t)w * q + g;
+    const uint2 sky_words = make_uint2((g == 0 ? 0u : sky_big) | (sky_big << 16), sky_big * 0x10001u);  // d = 0 costs nothing
     auto emit = [&](int j, uint64_t a, uint64_t b0, uint64_t b1, uint64_t b2, uint64_t b3) {
         const unsigned c0 = __popcll(a ^ b0), c1 = __popcll(a ^ b1), c2 = __popcll(a ^ b2), c3 = __popcll(a ^ b3);
-        out[(size_t)j * q] = make_uint2(c0 | (c1 << 16), c2 | (c3 << 16));
+        const bool masked = sky && __ldg(sky + j) == 255;
+        out[(size_t)j * q] = masked ? sky_words : make_uint2(c0 | (c1 << 16), c2 | (c3 << 16));
     };
     if (scale != 1) {  // general form: four look-ups per step
         for (int j = p; j < w; j += np) {
@@ -630,8 +643,8 @@ __global__ void __launch_bounds__(256) hamming_s16x2_kernel(const uint64_t* __re
     }
 }
 
-void launch_hamming_s16x2(const uint64_t* ct_l, const uint64_t* ct_r, void* cost, int views, int h, int w, int d, int scale,
-                          cudaStream_t st, LaunchCounter& lc) {
+void launch_hamming_s16x2(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r, unsigned sky_big, void* cost,
+                          int views, int h, int w, int d, int scale, cudaStream_t st, LaunchCounter& lc) {
     const size_t smem = (size_t)(2 * w + d) * sizeof(uint64_t);
     if (smem > 200 * 1024 || d % 4) {
         lc.err = cudaErrorInvalidValue;
@@ -639,7 +652,7 @@ void launch_hamming_s16x2(const uint64_t* ct_l, const uint64_t* ct_r, void* cost
         return;
     }
     if (smem > 48 * 1024) cudaFuncSetAttribute(hamming_s16x2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    hamming_s16x2_kernel<<<dim3(h, views), 256, smem, st>>>(ct_l, ct_r, static_cast<uint2*>(cost), h, w, d, scale);
+    hamming_s16x2_kernel<<<dim3(h, views), 256, smem, st>>>(ct_l, ct_r, sky_l, sky_r, sky_big, static_cast<uint2*>(cost), h, w, d, scale);
     lc.note("hamming_s16x2_kernel");
 }
 

@@ -281,7 +281,8 @@ int run_frame(sgm_engine* e, const uint8_t* left, size_t lstride, const uint8_t*
         launch_blur3(e->d_img, e->d_blur, h, w, st, lc);                                   // src/Solver.cpp:124-125
         launch_census(e->d_blur, e->d_census, h, w, p.census_h / s, p.census_w / s, st, lc);  // :127-139
         if (e->integer)
-            launch_hamming_s16x2(e->d_census, e->d_census + e->n, e->d_cost, e->views, h, w, D, s, st, lc);  // :143-248, raw
+            launch_hamming_s16x2(e->d_census, e->d_census + e->n, sky_l, sky_r, 2u * (unsigned)p.P2, e->d_cost, e->views, h, w, D, s, st,
+                                 lc);  // :143-248, raw; masked pixels: 2 * P2 stands in for 999999
         else {
         launch_hamming_hfilter(e->d_census, e->d_census + e->n, sky_l, sky_r, e->d_cost, e->views, h, w, D, s, p.box_w / s, st,
                                lc);                                                          // :143-248, :296-330
@@ -343,7 +344,9 @@ int check_images(sgm_engine* e, const void* left, size_t ls, const void* right, 
     if (!left || !right) return fail(e, SGM_ERR_INVALID, "left / right image is null");
     if (ls < (size_t)e->p.width || rs < (size_t)e->p.width) return fail(e, SGM_ERR_INVALID, "image stride smaller than width");
     if ((sl && sls < (size_t)e->iw) || (sr && srs < (size_t)e->iw)) return fail(e, SGM_ERR_INVALID, "sky mask stride smaller than width");
-    if (e->integer && (sl || sr)) return fail(e, SGM_ERR_UNSUPPORTED, "integer mode takes no sky masks (their 999999 fill does not fit 16 bits)");
+    // integer mode: a masked pixel's fill is 2 * P2 (stand-in of 999999), and 8 * (2 * P2 + P2) must fit 15 bits
+    if (e->integer && (sl || sr) && 24 * e->p.P2 > 32767)
+        return fail(e, SGM_ERR_UNSUPPORTED, "integer mode with sky masks needs P2 <= 1365 (the masked pixels' stand-in cost 2 * P2 must fit 16-bit sums)");
     if (e->busy) return fail(e, SGM_ERR_STATE, "a frame is already in flight on this handle: call sgm_wait first");
     return SGM_OK;
 }

@@ -41,10 +41,11 @@ void launch_census(const uint8_t* img /*[2][h*w]*/, uint64_t* table /*[2][h*w]*/
 void launch_hamming_hfilter(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r,
                             float* cost, int views, int h, int w, int d, int scale, int win, cudaStream_t st,
                             LaunchCounter& lc);
-// Integer mode: the raw Hamming volume (src/Solver.cpp:143-248 without sky mask or cost filter) as packed s16x2 words,
-// [views][h*w*d/2] 32-bit words.
-void launch_hamming_s16x2(const uint64_t* ct_l, const uint64_t* ct_r, void* cost, int views, int h, int w, int d, int scale,
-                          cudaStream_t st, LaunchCounter& lc);
+// Integer mode: the raw Hamming volume (src/Solver.cpp:143-248 without cost filter) as packed s16x2 words,
+// [views][h*w*d/2] 32-bit words.  Pixels masked by sky_l / sky_r (nullable; 255 = sky) cost 0 at d = 0 and sky_big elsewhere
+// (the 16-bit stand-in of the reference's 999999, see the kernel).
+void launch_hamming_s16x2(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r, unsigned sky_big, void* cost,
+                          int views, int h, int w, int d, int scale, cudaStream_t st, LaunchCounter& lc);
 // src/Solver.cpp:333-368 in place on `views` volumes.
 void launch_vfilter(float* cost, int views, int h, int w, int d, int win, cudaStream_t st, LaunchCounter& lc);
 // src/cost.cpp:4-30 (SAD) for every (pixel, d) of `views` views (view 1 = right view by symmetry).

@@ -69,8 +69,8 @@ void Solver::open_engine(int algo, int paths, int full_h, int full_w)
     p.speckle_dis = SPECKLE_DIS;
     if (const char *dev = std::getenv("SGM_B200_DEVICE")) p.device = std::atoi(dev);
     // Opt-in integer / DPX mode of the engine (include/sgm_b200.h: SGM_FLAG_INTEGER): SGM without the cost filter
-    // (COST_WIN_W = COST_WIN_H = 1 in the reference's terms) on 16-bit volumes.  It takes no sky masks; process() with
-    // masks then ends with the engine's error message, as every misuse does.
+    // (COST_WIN_W = COST_WIN_H = 1 in the reference's terms) on 16-bit volumes.  Sky masks are accepted like in the float
+    // mode (masked pixels cost 2 * P2 instead of 999999, with identical results: include/sgm_b200.h).
     if (algo == SGM_ALGO_SGM && std::getenv("SGM_B200_INTEGER")) {
         p.box_w = p.box_h = scale;
         p.flags |= SGM_FLAG_INTEGER;

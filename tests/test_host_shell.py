@@ -160,14 +160,15 @@ def test_node_style_driver_matches_oracle(algo, h, w, s, d, sky):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("h,w,s,d", [(96, 192, 1, 64), (120, 200, 2, 64)])
-def test_node_style_driver_integer_mode(h, w, s, d):
+@pytest.mark.parametrize("h,w,s,d,sky", [(96, 192, 1, 64, False), (120, 200, 2, 64, False), (120, 200, 1, 64, True)])
+def test_node_style_driver_integer_mode(h, w, s, d, sky):
     # SGM_B200_INTEGER=1: the C++ shell opens the engine in its integer / DPX mode (SGM without the cost filter);
-    # oracle = the restatement with the cost filter window at 1x1
+    # oracle = the restatement with the cost filter window at 1x1.  node.cpp:93 always passes sky masks: they are accepted.
     L, R, _ = synth.random_dot_pair(h, w, seed=h + d, bg=5, fg=min(17, d // 2), noise=15)
-    want = restate.process(L, R, s, d, "sgm", box_w=s, box_h=s)["f_final"]
+    masks = synth.sky_masks(h // s, w // s) if sky else None
+    want = restate.process(L, R, s, d, "sgm", *(masks or (None, None)), box_w=s, box_h=s)["f_final"]
     with tempfile.TemporaryDirectory() as tmp:
-        disp, disp2, _, _, _ = _run_driver(tmp, "sgm", h, w, s, d, L, R, None, env={"SGM_B200_INTEGER": "1"})
+        disp, disp2, _, _, _ = _run_driver(tmp, "sgm", h, w, s, d, L, R, masks, env={"SGM_B200_INTEGER": "1"})
     assert bits_equal(disp, want) and bits_equal(disp2, want)
 
 

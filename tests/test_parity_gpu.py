@@ -158,11 +158,35 @@ def test_integer_mode_rejects_what_it_cannot_represent():
     with pytest.raises(capi.SgmError) as e:
         capi.SGM(64, 64, 1, 32, flags=capi.FLAG_INTEGER, box_w=1, box_h=1)
     assert e.value.code == 2
-    sv = capi.SGM(64, 64, 1, 64, flags=capi.FLAG_INTEGER, box_w=1, box_h=1)
+    sv = capi.SGM(64, 64, 1, 64, flags=capi.FLAG_INTEGER, box_w=1, box_h=1, P2=2000)
     z = np.zeros((64, 64), np.uint8)
+    sv.process(z, z)                                                   # fine without masks (P2 <= 4033) ...
     with pytest.raises(capi.SgmError) as e:
-        sv.process(z, z, z, z)                                         # sky masks: 999999 does not fit 16 bits
+        sv.process(z, z, z, z)                                         # ... but the masked pixels' stand-in cost 2 * P2 needs P2 <= 1365
     assert e.value.code == 2
+    sv.close()
+
+
+@pytest.mark.parametrize("h,w,d,scale,P1,P2,frac", [(120, 200, 64, 1, 10, 100, 0.25), (97, 161, 128, 1, 7, 300, 0.4), (200, 320, 64, 2, 10, 100, 0.25),
+                                                    (64, 300, 128, 1, 10, 1365, 0.5)])
+def test_integer_mode_with_sky_masks_vs_oracle(h, w, d, scale, P1, P2, frac):
+    # the reference fills masked pixels with 999999 (src/Solver.cpp:165-179); the integer mode uses 2 * P2 and must still return
+    # the reference's results everywhere: checker = the float restatement (cost filter 1x1) with the same masks
+    L, R, _ = synth.random_dot_pair(h, w, seed=h * 3 + d, bg=3, fg=max(4, min(17, d // 2, w // 3)), noise=20)
+    sl, sr = synth.sky_masks(h // scale, w // scale, frac)
+    sr[:, : w // scale // 3] = 0                                       # the two masks differ
+    want = restate.process(L, R, scale, d, "sgm", sl, sr, taps=restate.ALL_TAPS, box_w=scale, box_h=scale, P1=P1, P2=P2)
+    sv = capi.SGM(h, w, scale, d, flags=capi.FLAG_INTEGER | capi.FLAG_KEEP_VOLUMES, box_w=scale, box_h=scale, P1=P1, P2=P2)
+    sv.process(L, R, sl, sr)
+    for v, m in ((0, sl), (1, sr)):
+        assert n_diff(sv.tap("disp", v), want["disp"][v]) == 0 and bits_equal(sv.tap("subpixel", v), want["fsub"][v])
+        free = m != 255                                                # the volumes agree wherever no mask applies ...
+        assert bits_equal(sv.tap("cost", v)[free], want["cost_hv"][v][free]) and bits_equal(sv.tap("pathsum", v)[free], want["S"][v][free])
+        c = sv.tap("cost", v)[~free]                                   # ... and masked pixels carry {0, 2 * P2, 2 * P2, ...}
+        assert (c[:, 0] == 0).all() and (c[:, 1:] == 2 * P2).all() and (want["cost_hv"][v][~free][:, 1:] == 999999).all()
+        assert (sv.tap("disp", v)[~free] == 0).all()                   # a masked pixel's winner is d = 0 and stays valid
+    assert bits_equal(sv.tap("lr"), want["f_lr"]) and bits_equal(sv.tap("median"), want["f_median"])
+    assert bits_equal(sv.get_disp(), want["f_final"])
     sv.close()
 
 
