@@ -138,51 +138,8 @@ struct RecBox {
     __device__ static __forceinline__ int last_filtered(int len) { return FIRST + (len - 2 * HALF) - 1; }
 };
 
-// src/Solver.cpp:143-248 (Hamming volume of one view, sky override) fused with :296-330 (horizontal filter).
-// One thread per (row, d) marches along j; a warp covers 32 consecutive d of one row, so the left census word
-// is a broadcast load, the right one a contiguous (reversed) 256-byte load, and every store is a coalesced
-// 128-byte line of the [i][j][d] volume.
-template <int WIN>
-__global__ void __launch_bounds__(128) hamming_hfilter_kernel(const uint64_t* __restrict__ ct_l,
-                                                              const uint64_t* __restrict__ ct_r,
-                                                              const uint8_t* __restrict__ sky_l,
-                                                              const uint8_t* __restrict__ sky_r,
-                                                              float* __restrict__ cost, int h, int w, int d, int scale) {
-    const int g = blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= h * d) return;
-    const int view = blockIdx.y;
-    const int i = g / d, k = g % d;
-    const int shift = k / scale;
-    const uint64_t* rl = ct_l + (size_t)i * w;
-    const uint64_t* rr = ct_r + (size_t)i * w;
-    const uint8_t* sky = view == 0 ? sky_l : sky_r;
-    const uint8_t* rs = sky ? sky + (size_t)i * w : nullptr;
-    float* out = cost + (size_t)view * h * w * d + (size_t)i * w * d + k;
-    const float sky_cost = k == 0 ? 0.0f : 999999.0f;
-    const int last = RecBox<WIN>::last_filtered(w);
-
-    RecBox<WIN> box;
-    box.reset();
-#pragma unroll 4
-    for (int j = 0; j < w; ++j) {
-        float c;
-        if (rs && __ldg(rs + j) == 255) {
-            c = sky_cost;  // src/Solver.cpp:165-179
-        } else if (view == 0) {
-            const int jr = max(j - shift, 0);  // src/Solver.cpp:185-189
-            c = (float)__popcll(__ldg(rl + j) ^ __ldg(rr + jr));
-        } else {
-            const int jl = min(j + shift, w - 1);  // src/Solver.cpp:239-243
-            c = (float)__popcll(__ldg(rl + jl) ^ __ldg(rr + j));
-        }
-        if (j < RecBox<WIN>::FIRST || j > last) out[(size_t)j * d] = c;  // unfiltered border columns
-        int pos;
-        float val;
-        if (box.feed(j, c, w, pos, val)) out[(size_t)pos * d] = val;
-    }
-}
-
-// The fused Hamming + horizontal filter kernel, one block per (row, view), one thread per disparity.  The two census
+// src/Solver.cpp:143-248 (Hamming volume of one view, sky override) fused with :296-330 (horizontal filter): one block per
+// (row, view), one thread per disparity.  The two census
 // rows are staged in shared memory once, padded by D entries of edge replication on the side the disparity shift runs
 // off (src/Solver.cpp:185 max(j - d, 0), :239 min(j + d, W - 1)), so the inner loop is two LDS.64, XOR, POPC and the
 // three-term recurrence; the steady state (columns WIN .. W-HALF-1) has no conditionals and keeps the last outputs in a
@@ -534,20 +491,13 @@ void launch_census(const uint8_t* img, uint64_t* table, int h, int w, int win_h,
     lc.note("census_kernel");
 }
 
+static size_t hamming_row_smem_bytes(int w, int d, bool sky) { return (size_t)(2 * w + d) * sizeof(uint64_t) + (sky ? (size_t)w : 0); }
+
 template <int WIN>
 static void launch_hh(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r, float* cost, int views,
                       int h, int w, int d, int scale, cudaStream_t st) {
-    bool legacy = false;  // the thread-per-(row, d) form below is the path of very wide rows; tuning builds can force it
-#ifdef SGM_B200_TUNING
-    legacy = std::getenv("SGM_B200_HFILTER_LEGACY") != nullptr;
-#endif
     const bool sky = sky_l || sky_r;
-    const size_t smem = (size_t)(2 * w + d) * sizeof(uint64_t) + (sky ? (size_t)w : 0);
-    if (legacy || smem > 200 * 1024) {  // very wide rows: the thread-per-(row, d) form that reads the tables through L1
-        dim3 grid((h * d + 127) / 128, views);
-        hamming_hfilter_kernel<WIN><<<grid, 128, 0, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale);
-        return;
-    }
+    const size_t smem = hamming_row_smem_bytes(w, d, sky);  // sgm_create rejects rows that do not fit (hamming_rows_fit)
     dim3 grid(h, views);
     if (sky) {
         if (smem > 48 * 1024) cudaFuncSetAttribute(hamming_hfilter_row_kernel<WIN, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -557,6 +507,8 @@ static void launch_hh(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t*
         hamming_hfilter_row_kernel<WIN, false><<<grid, d, smem, st>>>(ct_l, ct_r, sky_l, sky_r, cost, h, w, d, scale);
     }
 }
+
+bool hamming_rows_fit(int w, int d) { return hamming_row_smem_bytes(w, d, true) <= 200 * 1024; }
 
 void launch_hamming_hfilter(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r,
                             float* cost, int views, int h, int w, int d, int scale, int win, cudaStream_t st,

@@ -160,6 +160,7 @@ int sgm_create(sgm_engine** out, const sgm_params* params) {
         const int ch = p.census_h / p.scale, cw = p.census_w / p.scale;
         if (ch / 2 > 3 || cw / 2 > 4 || ch < 1 || cw < 1)
             return fail(nullptr, SGM_ERR_UNSUPPORTED, "census window / scale must fit 7x9");
+        if (!hamming_rows_fit(iw, p.max_disp)) return fail(nullptr, SGM_ERR_UNSUPPORTED, "working image too wide (%d) for the Hamming kernels' row staging", iw);
     } else {
         const int sh = p.sad_h / p.scale, sw = p.sad_w / p.scale;
         if (sh < 1 || sw < 1 || sh > 31 || sw > 31) return fail(nullptr, SGM_ERR_UNSUPPORTED, "SAD window / scale must be in 1..31");

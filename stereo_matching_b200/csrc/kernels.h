@@ -41,6 +41,9 @@ void launch_census(const uint8_t* img /*[2][h*w]*/, uint64_t* table /*[2][h*w]*/
 void launch_hamming_hfilter(const uint64_t* ct_l, const uint64_t* ct_r, const uint8_t* sky_l, const uint8_t* sky_r,
                             float* cost, int views, int h, int w, int d, int scale, int win, cudaStream_t st,
                             LaunchCounter& lc);
+// Both census rows of an image row (plus max_disp entries of padding) are staged in shared memory by the Hamming kernels:
+// false for images too wide for that (about 12,000 pixels at D = 256).
+bool hamming_rows_fit(int w, int d);
 // Integer mode: the raw Hamming volume (src/Solver.cpp:143-248 without cost filter) as packed s16x2 words,
 // [views][h*w*d/2] 32-bit words.  Pixels masked by sky_l / sky_r (nullable; 255 = sky) cost 0 at d = 0 and sky_big elsewhere
 // (the 16-bit stand-in of the reference's 999999, see the kernel).

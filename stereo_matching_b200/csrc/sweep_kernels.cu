@@ -419,8 +419,10 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
         for (int q = 0; q < LL::NCH; ++q) {
             const unsigned dst = rbase + slot * SLOT_BYTES + q * LL::CHUNK_SPAN * 4;
             cp_async_lane<LL::CW * 4>(dst, pc + q * LL::CHUNK_SPAN);
-            cp_async_lane<LL::CW * 4>(dst + VEC_BYTES, px + q * LL::CHUNK_SPAN);
-            if (DIAG || !UP) cp_async_lane<LL::CW * 4>(dst + 2 * VEC_BYTES, py + q * LL::CHUNK_SPAN);
+            if (!debug_skip(a, 4)) {  // (tuning build: bit 4 = do not fetch the A / B rows: WRONG results, LSU experiment)
+                cp_async_lane<LL::CW * 4>(dst + VEC_BYTES, px + q * LL::CHUNK_SPAN);
+                if (DIAG || !UP) cp_async_lane<LL::CW * 4>(dst + 2 * VEC_BYTES, py + q * LL::CHUNK_SPAN);
+            }
         }
         pc += rstep;
         px += rstep;
@@ -565,8 +567,13 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
                 }
                 // ---- outputs (overlap the other warps' arrival) ----
                 float X[E], Y[E];
-                lds_pixel<D>(rbase + u * SLOT_BYTES + VEC_BYTES, X);
-                if (DIAG || !UP) lds_pixel<D>(rbase + u * SLOT_BYTES + 2 * VEC_BYTES, Y);
+                if (!debug_skip(a, 8)) {  // (tuning build: bit 8 = do not read the A / B rows back from the ring: WRONG results)
+                    lds_pixel<D>(rbase + u * SLOT_BYTES + VEC_BYTES, X);
+                    if (DIAG || !UP) lds_pixel<D>(rbase + u * SLOT_BYTES + 2 * VEC_BYTES, Y);
+                } else {
+#pragma unroll
+                    for (int k = 0; k < E; ++k) X[k] = Y[k] = C[k];
+                }
                 if (!UP) {
                     float A[E];
 #pragma unroll

@@ -96,3 +96,11 @@ def test_no_cpu_fallback_without_a_device(lib):
     with pytest.raises(capi.SgmError) as e:
         capi.speckle_filter_static(1, 1, 64, 64, 65.0)
     assert e.value.code == 3
+
+
+def test_too_wide_rows_are_rejected_before_touching_the_device(lib):
+    # the Hamming kernels stage both census rows of an image row in shared memory: a row that does not fit is an unsupported
+    # shape (error code), not a slower path
+    with pytest.raises(capi.SgmError) as e:
+        capi.SGM(64, 14000, 1, 128)
+    assert e.value.code == 2 and "too wide" in str(e.value)
