@@ -798,6 +798,11 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
             case 11: return fused_impl<D, 8, SweepCfg<18, 6, 1>>(a, st, lc);
             case 12: return fused_impl<D, 8, SweepCfg<19, 4, 1>>(a, st, lc);
             case 13: return fused_impl<D, 8, typename DefaultCfg<D>::type>(a, st, lc);
+            case 14: return fused_impl<D, 8, SweepCfg<19, 6, 1>>(a, st, lc);
+            case 15: return fused_impl<D, 8, SweepCfg<19, 8, 1>>(a, st, lc);
+            case 16: return fused_impl<D, 8, SweepCfg<19, 2, 1>>(a, st, lc);
+            case 17: return fused_impl<D, 8, SweepCfg<16, 4, 1>>(a, st, lc);
+            case 18: return fused_impl<D, 8, SweepCfg<20, 4, 1>>(a, st, lc);
             default: break;
         }
     }
