@@ -517,3 +517,53 @@ def test_bm_sad_kitti_size_against_golden(golden_fullsize, name):
     assert not bad, f"{name}: taps whose hash differs from the restatement: {bad}"
     assert int((bm.get_disp() <= c["d"] - 1).sum()) == c["stats"]["valid"]
     bm.close()
+
+
+def _fuzz_cases(n, seed):
+    rng = np.random.RandomState(seed)
+    cases = []
+    for k in range(n):
+        algo = ("sgm", "sgm", "sgm_int", "bm", "bm_sad")[k % 5]
+        scale = int(rng.choice([1, 1, 2]))
+        d = int(rng.choice([64, 128] if algo == "sgm_int" else [32, 64, 128]))
+        h = int(rng.randint(16 * scale, 90 * scale))
+        w = int(rng.randint(16 * scale, 260 * scale))
+        cases.append(dict(algo=algo, h=h, w=w, d=d, scale=scale, noise=int(rng.choice([0, 5, 20, 60, 120])), sky=bool(rng.rand() < 0.4),
+                          paths=int(rng.choice([8, 8, 4])) if algo.startswith("sgm") else 8, median=int(rng.choice([5, 5, 3])),
+                          bg=int(rng.randint(0, 8)), fg=int(rng.randint(8, 30)), seed=int(rng.randint(1, 10 ** 6))))
+    return cases
+
+
+@pytest.mark.parametrize("c", _fuzz_cases(100, seed=20261105), ids=lambda c: f"{c['algo']}-{c['h']}x{c['w']}-d{c['d']}-s{c['scale']}")
+def test_fuzz_random_shapes_and_modes_vs_oracle(c):
+    # deterministic fuzzing over shapes (down to the 16x16 minimum, widths below D, odd sizes), scales, noise levels (none ..
+    # a third of the frame invalid), sky masks, 4 / 8 paths, both median windows and every pipeline, final and intermediate
+    # results against the oracle bit for bit
+    h, w, d, s = c["h"], c["w"], c["d"], c["scale"]
+    L, R, _ = synth.random_dot_pair(h, w, seed=c["seed"], bg=c["bg"], fg=min(c["fg"], max(1, w // s // 3)), noise=c["noise"])
+    sl, sr = synth.sky_masks(h // s, w // s, 0.3) if c["sky"] else (None, None)
+    over = dict(median_h=c["median"], median_w=c["median"])
+    if c["algo"] in ("sgm", "sgm_int"):
+        integer = c["algo"] == "sgm_int"
+        if integer:
+            over.update(box_w=s, box_h=s)
+        want = restate.process(L, R, s, d, "sgm", sl, sr, taps=restate.ALL_TAPS, paths=c["paths"], **over)
+        sv = capi.SGM(h, w, s, d, flags=(capi.FLAG_INTEGER if integer else 0), paths=c["paths"], **over)
+    else:
+        want = restate.process(L, R, s, d, c["algo"], sl, sr, taps=restate.ALL_TAPS, **over)
+        sv = (capi.BM if c["algo"] == "bm" else capi.BMSad)(h, w, s, d, **over)
+    sv.process(L, R, sl, sr)
+    bad = []
+    views = (0,) if c["algo"] == "bm" else (0, 1)
+    for v in views:
+        if n_diff(sv.tap("disp", v), want["disp"][v]):
+            bad.append(f"disp[{v}]")
+        if not bits_equal(sv.tap("subpixel", v), want["fsub"][v]):
+            bad.append(f"subpixel[{v}]")
+    for tap, key in (("lr", "f_lr"), ("median", "f_median")):
+        if not bits_equal(sv.tap(tap), want[key]):
+            bad.append(tap)
+    if not bits_equal(sv.get_disp(), want["f_final"]):
+        bad.append("final")
+    sv.close()
+    assert not bad, f"{c}: {bad}"
