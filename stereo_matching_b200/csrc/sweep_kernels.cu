@@ -327,11 +327,30 @@ __global__ void __launch_bounds__(WARPS * 32) sgm_hpair_async_kernel(const float
 // unrolled body and every shared-memory address is base + immediate.
 constexpr int SWEEP_DOWN = 0, SWEEP_UP = 1, SWEEP_UP_KEEP = 2;
 
+// Which column of the block a hardware warp works on (-1: none, the warp exits).  The two block-edge columns carry about a third
+// more work per row than the others (halo accept / publish, two recurrence steps one after the other) and every row ends at a
+// block barrier, so they set the pace.  A warp's scheduler is (hardware warp id) % 4.  Rule: the edge columns go to hardware
+// warps 3 and 7 (scheduler 3); the interior columns fill the warps of schedulers 0 - 2 in hardware order and use scheduler 3's
+// remaining warps (11, 15, ...) only when those are used up; whatever is left of the HWW >= NW hardware warps exits.  With
+// NW = HWW = 19 the schedulers host 5 + 5 + 5 interior warps and 2 edge + 2 interior; with NW = 17, HWW = 19 the edge warps
+// have scheduler 3 to themselves.  `identity`: tuning-build A/B switch (1242x375 D=128, NW = HWW = 19: 1.249 ms in natural
+// order, 1.196 ms with this rule).
+template <int NW, int HWW>
+__device__ __forceinline__ int sweep_column_of_warp(int hw, int nact, bool identity) {
+    static_assert(HWW >= NW, "one hardware warp per column at least");
+    if (identity || nact < 9 || NW < 16) return hw < nact ? hw : -1;
+    if (hw == 3) return 0;
+    if (hw == 7) return nact - 1;
+    constexpr int OUTSIDE = HWW - HWW / 4;  // hardware warps of schedulers 0 - 2
+    const int rank = (hw & 3) != 3 ? hw - ((hw + 1) >> 2) : OUTSIDE + ((hw - 11) >> 2);
+    return rank < nact - 2 ? 1 + rank : -1;  // interior columns 1 .. nact-2
+}
+
 // EDGE (compile-time copy of a warp-uniform fact): false = an interior warp — both diagonals come from shared memory and
 // neither restarts at an image border; such a warp carries none of the halo / border code (in the generic body those
 // ~35 instructions per pixel were issued predicated-off by 17 of 19 warps).  true = a block-edge or image-border warp.
 template <int D, int NW, int MODE, int PATHS, int PF, bool EDGE, class AR>
-__device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float* xmin, unsigned bar, float* sring) {
+__device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float* xmin, unsigned bar, float* sring, int wid) {
     constexpr bool UP = MODE != SWEEP_DOWN, KEEP_S = MODE == SWEEP_UP_KEEP;  // KEEP_S: also write the path sum S (debug tap)
     using LL = LaneLayout<D>;
     using HIO = HaloIO<D>;
@@ -339,12 +358,12 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
     constexpr bool DIAG = PATHS == 8;
     static_assert(NW >= 2 && PF % 2 == 0, "a block needs two columns; PF must be even");
     constexpr unsigned VEC_BYTES = D * 4, WARP_BYTES = 2 * VEC_BYTES, PAR_BYTES = NW * WARP_BYTES, MIN_PAR_BYTES = NW * 2 * 4;
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
     const int blk = blockIdx.x, nblk = gridDim.x;
     const int view = a.view0 + blockIdx.y;
     const int h = a.h, w = a.w;
-    const int j = blk * NW + wid;
     const int nact = min(NW, w - blk * NW);  // columns (= warps) of this block that exist
+    const int j = blk * NW + wid;             // "wid" is the COLUMN of the block this warp works on (sweep_column_of_warp)
 
     // ---- roles of the two diagonals of this warp ----
     const bool swap = EDGE && DIAG && wid == 0 && blk > 0;  // F = Pr (the left block waits for it), G = Pl (comes from the left block)
@@ -393,7 +412,11 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
     float Sp[E];
 #pragma unroll
     for (int k = 0; k < E; ++k) Sp[k] = 0.f;
+    // (tuning build, bit 32: the edge columns of a full block produce NO outputs — WRONG results; bounds what handing their
+    // sums / selection / stores to helper warps could gain)
+    const bool no_out = EDGE && nact >= 9 && debug_skip(a, 32);
     auto select_pending = [&](int rp) {  // rp = sweep row of the vector held in Sp
+        if (no_out) return;
         const WtaPick pk = AR::reduce(Sp, lane);
         if (lane == (rp & 31)) stash = pk;
     };
@@ -419,7 +442,7 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
         for (int q = 0; q < LL::NCH; ++q) {
             const unsigned dst = rbase + slot * SLOT_BYTES + q * LL::CHUNK_SPAN * 4;
             cp_async_lane<LL::CW * 4>(dst, pc + q * LL::CHUNK_SPAN);
-            if (!debug_skip(a, 4)) {  // (tuning build: bit 4 = do not fetch the A / B rows: WRONG results, LSU experiment)
+            if (!debug_skip(a, 4) && !no_out) {  // (tuning build: bit 4 = do not fetch the A / B rows: WRONG results, LSU experiment)
                 cp_async_lane<LL::CW * 4>(dst + VEC_BYTES, px + q * LL::CHUNK_SPAN);
                 if (DIAG || !UP) cp_async_lane<LL::CW * 4>(dst + 2 * VEC_BYTES, py + q * LL::CHUNK_SPAN);
             }
@@ -567,6 +590,8 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
                 }
                 // ---- outputs (overlap the other warps' arrival) ----
                 float X[E], Y[E];
+                if (no_out) {
+                } else
                 if (!debug_skip(a, 8)) {  // (tuning build: bit 8 = do not read the A / B rows back from the ring: WRONG results)
                     lds_pixel<D>(rbase + u * SLOT_BYTES + VEC_BYTES, X);
                     if (DIAG || !UP) lds_pixel<D>(rbase + u * SLOT_BYTES + 2 * VEC_BYTES, Y);
@@ -574,7 +599,8 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
 #pragma unroll
                     for (int k = 0; k < E; ++k) X[k] = Y[k] = C[k];
                 }
-                if (!UP) {
+                if (no_out) {
+                } else if (!UP) {
                     float A[E];
 #pragma unroll
                     for (int k = 0; k < E; ++k) A[k] = AR::add(AR::add(X[k], Y[k]), V[k]);  // (L1 + L2) + L3
@@ -615,42 +641,43 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
             }
         }
     }
-    if (UP) {  // drain the pipeline: the last row's selection and the rows still stashed
+    if (UP && !no_out) {  // drain the pipeline: the last row's selection and the rows still stashed
         select_pending(h - 1);
         flush_rows(h - 1);
     }
 }
 
-template <int D, int NW, int MODE, int PATHS, int PF, int MINB, class AR>
-__global__ void __launch_bounds__(NW * 32, MINB) sgm_sweep_kernel(const SweepArgs a) {
+template <int D, int NW, int MODE, int PATHS, int PF, int MINB, class AR, int HWW = NW>
+__global__ void __launch_bounds__(HWW * 32, MINB) sgm_sweep_kernel(const SweepArgs a) {
     constexpr bool DIAG = PATHS == 8;
     __shared__ __align__(16) float xch[DIAG ? 2 * NW * 2 * D : 4];  // [parity][warp][0 = Pl, 1 = Pr][d]
     __shared__ float xmin[DIAG ? 2 * NW * 2 : 1];                   // [parity][warp][0 = Pl, 1 = Pr] min of the vector
     __shared__ __align__(8) unsigned long long bar_mem;
     extern __shared__ __align__(16) float sring[];  // [NW][PF][3][D]
-    const int wid = threadIdx.x >> 5, blk = blockIdx.x;
+    const int blk = blockIdx.x;
     const int nact = min(NW, a.w - blk * NW);  // columns (= warps) of this block that exist
     const unsigned bar = smem_u32(&bar_mem);
     if (DIAG) {
         if (threadIdx.x == 0) mbar_init(bar, nact);  // one arrival per active warp and row
         __syncthreads();
     }
-    if (wid >= nact) return;
+    const int wid = sweep_column_of_warp<NW, HWW>(threadIdx.x >> 5, nact, debug_skip(a, 16));
+    if (wid < 0) return;  // a spare hardware warp, or a column beyond the image
     const int j = blk * NW + wid;
     // block-edge warps (they exchange with a neighbouring block) and image-border columns take the general body
     const bool edge = DIAG && (wid == 0 || wid == nact - 1 || j == 0 || j == a.w - 1);
     if (edge)
-        sweep_body<D, NW, MODE, PATHS, PF, true, AR>(a, xch, xmin, bar, sring);
+        sweep_body<D, NW, MODE, PATHS, PF, true, AR>(a, xch, xmin, bar, sring, wid);
     else
-        sweep_body<D, NW, MODE, PATHS, PF, false, AR>(a, xch, xmin, bar, sring);
+        sweep_body<D, NW, MODE, PATHS, PF, false, AR>(a, xch, xmin, bar, sring, wid);
 }
 
 constexpr int SWEEP_NW = 8;  // smallest block width in columns (sizes the halo ring)
 
 // Launch shape of the sweeps: NW columns (warps) per block, PF rows in flight per warp, MINB blocks per SM.
-template <int NW_, int PF_, int MINB_>
+template <int NW_, int PF_, int MINB_, int HWW_ = NW_>
 struct SweepCfg {
-    static constexpr int NW = NW_, PF = PF_, MINB = MINB_;
+    static constexpr int NW = NW_, PF = PF_, MINB = MINB_, HWW = HWW_;  // HWW: hardware warps per block (>= NW: spare warps idle)
 };
 
 template <int D, class CFG>
@@ -660,16 +687,16 @@ constexpr size_t sweep_ring_bytes() {
 
 template <int D, int MODE, int PATHS, class CFG, class AR>
 cudaError_t launch_sweep(const SweepArgs& sa, int nblk, int views, bool cooperative, cudaStream_t st) {
-    auto kern = sgm_sweep_kernel<D, CFG::NW, MODE, PATHS, CFG::PF, CFG::MINB, AR>;
+    auto kern = sgm_sweep_kernel<D, CFG::NW, MODE, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW>;
     constexpr size_t ring_bytes = sweep_ring_bytes<D, CFG>();
     cudaError_t attr = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes);  // per device: cheap, so always
     if (attr != cudaSuccess) return attr;
     if (!cooperative) {
-        kern<<<dim3(nblk, views), CFG::NW * 32, ring_bytes, st>>>(sa);
+        kern<<<dim3(nblk, views), CFG::HWW * 32, ring_bytes, st>>>(sa);
         return cudaGetLastError();
     }
     void* params[] = {const_cast<SweepArgs*>(&sa)};
-    return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(nblk, views), dim3(CFG::NW * 32), params, ring_bytes, st);
+    return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(nblk, views), dim3(CFG::HWW * 32), params, ring_bytes, st);
 }
 
 template <int D, int PATHS, class CFG, class AR>
@@ -682,11 +709,11 @@ int sweep_capacity(int device) {
     // the ring may exceed the default 48 KB of dynamic shared memory: opt in before asking for the occupancy
     auto ask = [&](auto kern, int& out) {
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<D, CFG>());
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&out, kern, CFG::NW * 32, sweep_ring_bytes<D, CFG>());
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&out, kern, CFG::HWW * 32, sweep_ring_bytes<D, CFG>());
     };
-    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_DOWN, PATHS, CFG::PF, CFG::MINB, AR>, per_sm[0]);
-    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP, PATHS, CFG::PF, CFG::MINB, AR>, per_sm[1]);
-    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP_KEEP, PATHS, CFG::PF, CFG::MINB, AR>, per_sm[2]);
+    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_DOWN, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW>, per_sm[0]);
+    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW>, per_sm[1]);
+    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP_KEEP, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW>, per_sm[2]);
     const int least = per_sm[0] < per_sm[1] ? (per_sm[0] < per_sm[2] ? per_sm[0] : per_sm[2]) : (per_sm[1] < per_sm[2] ? per_sm[1] : per_sm[2]);
     const int cap = coop ? sms * least : 0;
     if (device >= 0 && device < 16) cached[device] = cap + 1;
@@ -779,7 +806,7 @@ template <int D>
 bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
     if (a.paths != 8) return fused_impl<D, 4, typename DefaultCfg<D>::type>(a, st, lc);
 #ifdef SGM_B200_TUNING
-    if constexpr (D == 128) {
+    if constexpr (D == 128 || D == 64) {
         static const int cfg = [] {
             const char* e = std::getenv("SGM_B200_SWEEP_CFG");
             return e ? std::atoi(e) : 0;
@@ -803,6 +830,17 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
             case 16: return fused_impl<D, 8, SweepCfg<19, 2, 1>>(a, st, lc);
             case 17: return fused_impl<D, 8, SweepCfg<16, 4, 1>>(a, st, lc);
             case 18: return fused_impl<D, 8, SweepCfg<20, 4, 1>>(a, st, lc);
+            case 19: return fused_impl<D, 8, SweepCfg<17, 4, 1, 17>>(a, st, lc);  // schedulers host 5 4 4 | 2 edge + 2
+            case 20: return fused_impl<D, 8, SweepCfg<17, 4, 1, 18>>(a, st, lc);  // 5 5 4 | 2 + 1
+            case 21: return fused_impl<D, 8, SweepCfg<17, 4, 1, 19>>(a, st, lc);  // 5 5 5 | 2
+            case 22: return fused_impl<D, 8, SweepCfg<18, 4, 1, 20>>(a, st, lc);  // 5 5 5 | 2 + 1
+            case 23: return fused_impl<D, 8, SweepCfg<17, 6, 1, 19>>(a, st, lc);
+            case 24: return fused_impl<D, 8, SweepCfg<17, 2, 1, 19>>(a, st, lc);
+            case 25: return fused_impl<D, 8, SweepCfg<18, 4, 1, 18>>(a, st, lc);  // 5 5 4 | 2 + 2
+            case 26: return fused_impl<D, 8, SweepCfg<17, 2, 1, 18>>(a, st, lc);
+            case 27: return fused_impl<D, 8, SweepCfg<17, 2, 1, 17>>(a, st, lc);
+            case 28: return fused_impl<D, 8, SweepCfg<18, 2, 1, 20>>(a, st, lc);
+            case 29: return fused_impl<D, 8, SweepCfg<18, 2, 1, 18>>(a, st, lc);
             default: break;
         }
     }
@@ -845,6 +883,12 @@ bool fused_dispatch_packed(const AggregateArgs& a0, cudaStream_t st, LaunchCount
         case 4: return fused_impl<DW, 8, SweepCfg<19, 6, 1>, AR>(a, st, lc);
         case 5: return fused_impl<DW, 8, SweepCfg<17, 4, 1>, AR>(a, st, lc);
         case 6: return fused_impl<DW, 8, SweepCfg<9, 4, 2>, AR>(a, st, lc);
+        case 7: return fused_impl<DW, 8, SweepCfg<17, 4, 1, 19>, AR>(a, st, lc);
+        case 8: return fused_impl<DW, 8, SweepCfg<18, 4, 1, 20>, AR>(a, st, lc);
+        case 9: return fused_impl<DW, 8, SweepCfg<17, 4, 1, 18>, AR>(a, st, lc);
+        case 10: return fused_impl<DW, 8, SweepCfg<17, 2, 1, 19>, AR>(a, st, lc);
+        case 11: return fused_impl<DW, 8, SweepCfg<19, 2, 1, 19>, AR>(a, st, lc);
+        case 12: return fused_impl<DW, 8, SweepCfg<17, 2, 1, 18>, AR>(a, st, lc);
         default: break;
     }
 #endif
