@@ -327,30 +327,44 @@ __global__ void __launch_bounds__(WARPS * 32) sgm_hpair_async_kernel(const float
 // unrolled body and every shared-memory address is base + immediate.
 constexpr int SWEEP_DOWN = 0, SWEEP_UP = 1, SWEEP_UP_KEEP = 2;
 
-// Which column of the block a hardware warp works on (-1: none, the warp exits).  The two block-edge columns carry about a third
-// more work per row than the others (halo accept / publish, two recurrence steps one after the other) and every row ends at a
-// block barrier, so they set the pace.  A warp's scheduler is (hardware warp id) % 4.  Rule: the edge columns go to hardware
-// warps 3 and 7 (scheduler 3); the interior columns fill the warps of schedulers 0 - 2 in hardware order and use scheduler 3's
-// remaining warps (11, 15, ...) only when those are used up; whatever is left of the HWW >= NW hardware warps exits.  With
-// NW = HWW = 19 the schedulers host 5 + 5 + 5 interior warps and 2 edge + 2 interior; with NW = 17, HWW = 19 the edge warps
-// have scheduler 3 to themselves.  `identity`: tuning-build A/B switch (1242x375 D=128, NW = HWW = 19: 1.249 ms in natural
-// order, 1.196 ms with this rule).
-template <int NW, int HWW>
+// Which column of the block a hardware warp works on (-1: none, the warp exits; NW + e: HELPER of edge column e, below).
+// The two block-edge columns carry about a third more work per row than the others (halo accept / publish, two recurrence
+// steps one after the other) and every row ends at a block barrier, so they set the pace.  A warp's scheduler is
+// (hardware warp id) % 4.  Rule: the edge columns go to hardware warps 3 and 7 (scheduler 3) and, with HELP, their helper
+// warps to 11 and 15; the interior columns fill the warps of schedulers 0 - 2 in hardware order and use scheduler 3's
+// remaining warps only when those are used up; whatever is left of the HWW hardware warps exits.  With NW = HWW = 19 the
+// schedulers host 5 + 5 + 5 interior warps and 2 edge + 2 interior; with NW = 17, HWW = 19 scheduler 3 belongs to the edge
+// warps (and their helpers).  `identity`: tuning-build A/B switch (1242x375 D=128, NW = HWW = 19: 1.249 ms in natural
+// order, 1.196 ms with this rule).  Blocks of fewer than 9 columns (the ragged last block of a row) use the natural order.
+template <int NW, int HWW, bool HELP>
 __device__ __forceinline__ int sweep_column_of_warp(int hw, int nact, bool identity) {
-    static_assert(HWW >= NW, "one hardware warp per column at least");
+    static_assert(HWW >= NW + (HELP ? 2 : 0), "one hardware warp per column (and helper) at least");
+    static_assert(!HELP || NW >= 16, "helper warps sit on hardware warps 11 and 15");
     if (identity || nact < 9 || NW < 16) return hw < nact ? hw : -1;
     if (hw == 3) return 0;
     if (hw == 7) return nact - 1;
-    constexpr int OUTSIDE = HWW - HWW / 4;  // hardware warps of schedulers 0 - 2
-    const int rank = (hw & 3) != 3 ? hw - ((hw + 1) >> 2) : OUTSIDE + ((hw - 11) >> 2);
+    if (HELP && hw == 11) return NW;
+    if (HELP && hw == 15) return NW + 1;
+    constexpr int OUTSIDE = HWW - HWW / 4;      // hardware warps of schedulers 0 - 2
+    constexpr int FIRST3 = HELP ? 19 : 11;      // first hardware warp of scheduler 3 that may take an interior column
+    const int rank = (hw & 3) != 3 ? hw - ((hw + 1) >> 2) : OUTSIDE + ((hw - FIRST3) >> 2);
     return rank < nact - 2 ? 1 + rank : -1;  // interior columns 1 .. nact-2
+}
+// Do the edge columns of this block hand their output work to helper warps?  (warp-uniform, the same answer in every warp)
+template <bool HELP>
+__device__ __forceinline__ bool sweep_block_has_helpers(int nact, bool identity) {
+    return HELP && !identity && nact >= 9;
 }
 
 // EDGE (compile-time copy of a warp-uniform fact): false = an interior warp — both diagonals come from shared memory and
 // neither restarts at an image border; such a warp carries none of the halo / border code (in the generic body those
 // ~35 instructions per pixel were issued predicated-off by 17 of 19 warps).  true = a block-edge or image-border warp.
-template <int D, int NW, int MODE, int PATHS, int PF, bool EDGE, class AR>
-__device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float* xmin, unsigned bar, float* sring, int wid) {
+// OFFL (edge warps of a block with helpers only): this warp runs the recurrences and the exchanges; its sums, selection and
+// stores are done by its helper warp (sweep_helper_body), which gets the vertical path's vector through `vx`.
+template <int D, int NW, int MODE, int PATHS, int PF, bool EDGE, class AR, bool OFFL = false>
+__device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float* xmin, unsigned bar, float* sring, int wid,
+                                           float* vx = nullptr) {
+    static_assert(!OFFL || EDGE, "only edge warps have helpers");
     constexpr bool UP = MODE != SWEEP_DOWN, KEEP_S = MODE == SWEEP_UP_KEEP;  // KEEP_S: also write the path sum S (debug tap)
     using LL = LaneLayout<D>;
     using HIO = HaloIO<D>;
@@ -414,7 +428,8 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
     for (int k = 0; k < E; ++k) Sp[k] = 0.f;
     // (tuning build, bit 32: the edge columns of a full block produce NO outputs — WRONG results; bounds what handing their
     // sums / selection / stores to helper warps could gain)
-    const bool no_out = EDGE && nact >= 9 && debug_skip(a, 32);
+    const bool no_out = OFFL || (EDGE && nact >= 9 && debug_skip(a, 32));
+    const unsigned v_dst = OFFL ? smem_u32(vx) + (wid == 0 ? 0u : VEC_BYTES) + lane * LL::CW * 4 : 0u;  // [parity][edge][d]
     auto select_pending = [&](int rp) {  // rp = sweep row of the vector held in Sp
         if (no_out) return;
         const WtaPick pk = AR::reduce(Sp, lane);
@@ -582,6 +597,7 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
                         sts_f32(gm_dst + par * MIN_PAR_BYTES, mP[2]);
                     }
                 }
+                if (OFFL) sts_pixel<D>(v_dst + par * 2 * VEC_BYTES, V);
                 if (DIAG) {
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar);  // this warp's row r vectors are published
@@ -647,26 +663,159 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
     }
 }
 
-template <int D, int NW, int MODE, int PATHS, int PF, int MINB, class AR, int HWW = NW>
+// Helper warp of a block-edge column (which = 0: the block's first column, 1: its last).  The edge warps are the critical path
+// of the block (see sweep_column_of_warp); everything of their pixel that the NEXT row does not wait for is done here
+// instead: the row's A / B vectors come through this warp's own cp.async ring, the three path vectors of the row from shared
+// memory (F and G are published there for the neighbouring columns anyway, V through `vx`), then the same sums, selection
+// and stores as sweep_body, in the same order.  The helper takes part in the row barrier: its arrival for row r + 1 says
+// "row r has been read", which is what allows row r + 2 to overwrite the same parity.
+template <int D, int NW, int MODE, int PF, class AR>
+__device__ __forceinline__ void sweep_helper_body(const SweepArgs& a, const float* xch, const float* vx, unsigned bar, float* sring,
+                                                  int which, int nact) {
+    constexpr bool UP = MODE != SWEEP_DOWN, KEEP_S = MODE == SWEEP_UP_KEEP;
+    using LL = LaneLayout<D>;
+    constexpr int E = LL::E;
+    static_assert(PF % 2 == 0, "PF must be even");
+    constexpr unsigned VEC_BYTES = D * 4, WARP_BYTES = 2 * VEC_BYTES, PAR_BYTES = NW * WARP_BYTES, SLOT_BYTES = 3 * VEC_BYTES;
+    const int lane = threadIdx.x & 31;
+    const int blk = blockIdx.x;
+    const int view = a.view0 + blockIdx.y;
+    const int h = a.h, w = a.w;
+    const int col = which ? nact - 1 : 0;
+    const int j = blk * NW + col;
+    const bool swap = col == 0 && blk > 0;  // as in sweep_body: slot 0 / 1 of the column hold F / G = Pr / Pl instead of Pl / Pr
+    const int f_id = swap ? 1 : 0, g_id = swap ? 0 : 1;
+    const unsigned lane_off = lane * LL::CW * 4;
+    const unsigned f_src = smem_u32(xch) + col * WARP_BYTES + f_id * VEC_BYTES + lane_off;
+    const unsigned g_src = smem_u32(xch) + col * WARP_BYTES + g_id * VEC_BYTES + lane_off;
+    const unsigned v_src = smem_u32(vx) + which * VEC_BYTES + lane_off;
+
+    const ptrdiff_t rstep = UP ? -(ptrdiff_t)w * D : (ptrdiff_t)w * D;
+    const size_t first = ((size_t)(UP ? h - 1 : 0) * w + j) * D + lane * LL::CW;
+    const float* px = a.acc_a + view * a.vol_stride + first;
+    const float* py = a.acc_b + view * a.vol_stride + first;
+    float* oa = a.acc_a + view * a.vol_stride + first;
+    float* ob = !UP ? a.acc_b + view * a.vol_stride + first : nullptr;
+    float* os = KEEP_S ? a.pathsum + view * a.vol_stride + first : nullptr;
+    const ptrdiff_t pstep = UP ? -(ptrdiff_t)w : (ptrdiff_t)w;
+    const size_t opix0 = view * a.img_stride + (size_t)(UP ? h - 1 : 0) * w + j;
+    WtaPick stash = {};
+    auto flush_rows = [&](int rlast) {  // as in sweep_body
+        const int rr = (rlast & ~31) + lane;
+        if (rr <= rlast) {
+            int dd;
+            float sub;
+            wta_finish<AR::DISP>(stash, a.ratio, a.min_gap, true, dd, sub);
+            const size_t o = opix0 + (ptrdiff_t)rr * pstep;
+            a.disp[o] = (uint16_t)dd;
+            a.subpixel[o] = sub;
+        }
+    };
+    const unsigned rbase = smem_u32(sring) + (unsigned)(NW + which) * PF * SLOT_BYTES + lane_off;  // the rings after the columns'
+    auto fetch = [&](int slot) {
+#pragma unroll
+        for (int q = 0; q < LL::NCH; ++q) {
+            const unsigned dst = rbase + slot * SLOT_BYTES + q * LL::CHUNK_SPAN * 4;
+            cp_async_lane<LL::CW * 4>(dst + VEC_BYTES, px + q * LL::CHUNK_SPAN);
+            cp_async_lane<LL::CW * 4>(dst + 2 * VEC_BYTES, py + q * LL::CHUNK_SPAN);
+        }
+        px += rstep;
+        py += rstep;
+    };
+#pragma unroll
+    for (int u = 0; u < PF; ++u) {
+        if (u < h) fetch(u);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    if (lane == 0) mbar_arrive(bar);  // row 0: nothing read yet
+    for (int r0 = 0; r0 < h; r0 += PF) {
+#pragma unroll
+        for (int u = 0; u < PF; ++u) {
+            const int r = r0 + u;
+            if (r < h) {
+                const unsigned par = u & 1;  // == r & 1
+                float F[E], G[E], V[E], X[E], Y[E];
+                asm volatile("cp.async.wait_group %0;" ::"n"(PF - 1) : "memory");
+                mbar_wait(bar, par, a.error);  // every warp's row r vectors are in shared memory
+                lds_pixel<D>(f_src + par * PAR_BYTES, F);
+                lds_pixel<D>(g_src + par * PAR_BYTES, G);
+                lds_pixel<D>(v_src + par * 2 * VEC_BYTES, V);
+                lds_pixel<D>(rbase + u * SLOT_BYTES + VEC_BYTES, X);
+                lds_pixel<D>(rbase + u * SLOT_BYTES + 2 * VEC_BYTES, Y);
+                if (r + 1 < h) {  // arrival for row r + 1: row r has been read (the loads above are complete: F feeds the fence)
+                    float keep = F[0] + G[0] + V[0];
+                    asm volatile("" ::"f"(keep) : "memory");
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar);
+                }
+                if (!UP) {
+                    float A[E], B[E];
+#pragma unroll
+                    for (int k = 0; k < E; ++k) A[k] = AR::add(AR::add(X[k], Y[k]), V[k]);  // (L1 + L2) + L3
+                    stg_vec<D>(oa, A);
+#pragma unroll
+                    for (int k = 0; k < E; ++k) B[k] = AR::add(F[k], G[k]);  // L5 + L6
+                    stg_vec<D>(ob, B);
+                    oa += rstep;
+                    ob += rstep;
+                } else {
+                    float S[E];
+                    if (!swap) {
+#pragma unroll
+                        for (int k = 0; k < E; ++k)  // (A + L4) + ((B + L7) + L8), src/SGM.cpp:386-390
+                            S[k] = AR::add(AR::add(X[k], V[k]), AR::add(AR::add(Y[k], F[k]), G[k]));
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < E; ++k)
+                            S[k] = AR::add(AR::add(X[k], V[k]), AR::add(AR::add(Y[k], G[k]), F[k]));
+                    }
+                    if (KEEP_S) {
+                        stg_vec<D>(os, S);
+                        os += rstep;
+                    }
+                    const WtaPick pk = AR::reduce(S, lane);
+                    if (lane == (r & 31)) stash = pk;
+                    if ((r & 31) == 31) flush_rows(r);
+                }
+                if (r + PF < h) fetch(u);
+                asm volatile("cp.async.commit_group;" ::: "memory");
+            }
+        }
+    }
+    if (UP && ((h - 1) & 31) != 31) flush_rows(h - 1);
+}
+
+template <int D, int NW, int MODE, int PATHS, int PF, int MINB, class AR, int HWW = NW, bool HELP = false>
 __global__ void __launch_bounds__(HWW * 32, MINB) sgm_sweep_kernel(const SweepArgs a) {
     constexpr bool DIAG = PATHS == 8;
+    static_assert(!HELP || DIAG, "helper warps exist for the 8-path sweeps only");
     __shared__ __align__(16) float xch[DIAG ? 2 * NW * 2 * D : 4];  // [parity][warp][0 = Pl, 1 = Pr][d]
     __shared__ float xmin[DIAG ? 2 * NW * 2 : 1];                   // [parity][warp][0 = Pl, 1 = Pr] min of the vector
+    __shared__ __align__(16) float vx[HELP ? 2 * 2 * D : 4];        // [parity][edge column][d]: vertical path, for the helper warps
     __shared__ __align__(8) unsigned long long bar_mem;
-    extern __shared__ __align__(16) float sring[];  // [NW][PF][3][D]
+    extern __shared__ __align__(16) float sring[];  // [NW (+ 2 helpers)][PF][3][D]
     const int blk = blockIdx.x;
     const int nact = min(NW, a.w - blk * NW);  // columns (= warps) of this block that exist
+    const bool helpers = sweep_block_has_helpers<HELP>(nact, debug_skip(a, 16));
     const unsigned bar = smem_u32(&bar_mem);
     if (DIAG) {
-        if (threadIdx.x == 0) mbar_init(bar, nact);  // one arrival per active warp and row
+        if (threadIdx.x == 0) mbar_init(bar, nact + (helpers ? 2 : 0));  // one arrival per active warp and row
         __syncthreads();
     }
-    const int wid = sweep_column_of_warp<NW, HWW>(threadIdx.x >> 5, nact, debug_skip(a, 16));
+    const int wid = sweep_column_of_warp<NW, HWW, HELP>(threadIdx.x >> 5, nact, debug_skip(a, 16));
     if (wid < 0) return;  // a spare hardware warp, or a column beyond the image
+    if constexpr (HELP) {
+        if (wid >= NW) {
+            sweep_helper_body<D, NW, MODE, PF, AR>(a, xch, vx, bar, sring, wid - NW, nact);
+            return;
+        }
+    }
     const int j = blk * NW + wid;
     // block-edge warps (they exchange with a neighbouring block) and image-border columns take the general body
     const bool edge = DIAG && (wid == 0 || wid == nact - 1 || j == 0 || j == a.w - 1);
-    if (edge)
+    if (HELP && edge && helpers)
+        sweep_body<D, NW, MODE, PATHS, PF, true, AR, HELP>(a, xch, xmin, bar, sring, wid, vx);
+    else if (edge)
         sweep_body<D, NW, MODE, PATHS, PF, true, AR>(a, xch, xmin, bar, sring, wid);
     else
         sweep_body<D, NW, MODE, PATHS, PF, false, AR>(a, xch, xmin, bar, sring, wid);
@@ -675,19 +824,20 @@ __global__ void __launch_bounds__(HWW * 32, MINB) sgm_sweep_kernel(const SweepAr
 constexpr int SWEEP_NW = 8;  // smallest block width in columns (sizes the halo ring)
 
 // Launch shape of the sweeps: NW columns (warps) per block, PF rows in flight per warp, MINB blocks per SM.
-template <int NW_, int PF_, int MINB_, int HWW_ = NW_>
+template <int NW_, int PF_, int MINB_, int HWW_ = NW_, bool HELP_ = false>
 struct SweepCfg {
     static constexpr int NW = NW_, PF = PF_, MINB = MINB_, HWW = HWW_;  // HWW: hardware warps per block (>= NW: spare warps idle)
+    static constexpr bool HELP = HELP_;  // two of the spare warps do the output work of the block-edge columns (8 paths)
 };
 
 template <int D, class CFG>
 constexpr size_t sweep_ring_bytes() {
-    return (size_t)CFG::NW * CFG::PF * 3 * D * sizeof(float);
+    return (size_t)(CFG::NW + (CFG::HELP ? 2 : 0)) * CFG::PF * 3 * D * sizeof(float);
 }
 
 template <int D, int MODE, int PATHS, class CFG, class AR>
 cudaError_t launch_sweep(const SweepArgs& sa, int nblk, int views, bool cooperative, cudaStream_t st) {
-    auto kern = sgm_sweep_kernel<D, CFG::NW, MODE, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW>;
+    auto kern = sgm_sweep_kernel<D, CFG::NW, MODE, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW, CFG::HELP>;
     constexpr size_t ring_bytes = sweep_ring_bytes<D, CFG>();
     cudaError_t attr = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes);  // per device: cheap, so always
     if (attr != cudaSuccess) return attr;
@@ -711,9 +861,9 @@ int sweep_capacity(int device) {
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<D, CFG>());
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&out, kern, CFG::HWW * 32, sweep_ring_bytes<D, CFG>());
     };
-    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_DOWN, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW>, per_sm[0]);
-    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW>, per_sm[1]);
-    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP_KEEP, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW>, per_sm[2]);
+    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_DOWN, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW, CFG::HELP>, per_sm[0]);
+    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW, CFG::HELP>, per_sm[1]);
+    ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP_KEEP, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW, CFG::HELP>, per_sm[2]);
     const int least = per_sm[0] < per_sm[1] ? (per_sm[0] < per_sm[2] ? per_sm[0] : per_sm[2]) : (per_sm[1] < per_sm[2] ? per_sm[1] : per_sm[2]);
     const int cap = coop ? sms * least : 0;
     if (device >= 0 && device < 16) cached[device] = cap + 1;
@@ -802,11 +952,46 @@ struct DefaultCfg<128> {
     using type = SweepCfg<10, 4, 2>;  // 1242x375: 250 blocks of 10 columns, 2 per SM
 };
 
+// Automatic shape for up to 128 words per pixel: when the default would put two blocks on some SMs and one on others (rows
+// advance in lock-step, so the crowded SMs set the pace), prefer ONE wide block per SM.  Both wide shapes run 19 hardware
+// warps (more would put six warps on one scheduler's register file: 80 registers instead of 96, heavy spills) and keep two
+// rows in flight per warp (four cost more spill traffic in the up sweep than they hide latency).
+//   Wide17: 17 columns; the two block-edge warps have a warp scheduler to themselves (sweep_column_of_warp).
+//           KITTI width: 2 x 74 blocks = one per SM of a B200.  1242x375 D=128: aggregation 1.14 ms.
+//   Wide19: 19 columns, for widths whose 17-column grid does not fit the device (edge warps share their scheduler with two
+//           interior warps; 1242x375 D=128: 1.20 ms).
+using Wide17 = SweepCfg<17, 2, 1, 19>;
+using Wide19 = SweepCfg<19, 2, 1, 19>;
+template <class Def>
+int wide_shape(int views, int w) {
+    int device = 0, sms = 0;
+    cudaGetDevice(&device);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    const int def_blocks = views * ((w + Def::NW - 1) / Def::NW);
+    if (def_blocks <= sms) return 0;  // the default shape already has at most one block per SM
+    if (views * ((w + Wide17::NW - 1) / Wide17::NW) <= sms) return 17;
+    if (views * ((w + Wide19::NW - 1) / Wide19::NW) <= sms - 12) return 19;
+    return 0;
+}
+
 template <int D>
 bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
     if (a.paths != 8) return fused_impl<D, 4, typename DefaultCfg<D>::type>(a, st, lc);
 #ifdef SGM_B200_TUNING
-    if constexpr (D == 128 || D == 64) {
+    if constexpr (D == 64) {  // a short list for D = 64 (every entry costs three kernels of compile time)
+        static const int cfg64 = [] {
+            const char* e = std::getenv("SGM_B200_SWEEP_CFG");
+            return e ? std::atoi(e) : 0;
+        }();
+        switch (cfg64) {
+            case 16: return fused_impl<D, 8, SweepCfg<19, 2, 1>>(a, st, lc);
+            case 24: return fused_impl<D, 8, SweepCfg<17, 2, 1, 19>>(a, st, lc);
+            case 30: return fused_impl<D, 8, SweepCfg<17, 2, 1, 19, true>>(a, st, lc);
+            case 34: return fused_impl<D, 8, SweepCfg<17, 4, 1, 19, true>>(a, st, lc);
+            default: break;
+        }
+    }
+    if constexpr (D == 128) {
         static const int cfg = [] {
             const char* e = std::getenv("SGM_B200_SWEEP_CFG");
             return e ? std::atoi(e) : 0;
@@ -841,21 +1026,20 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
             case 27: return fused_impl<D, 8, SweepCfg<17, 2, 1, 17>>(a, st, lc);
             case 28: return fused_impl<D, 8, SweepCfg<18, 2, 1, 20>>(a, st, lc);
             case 29: return fused_impl<D, 8, SweepCfg<18, 2, 1, 18>>(a, st, lc);
+            case 30: return fused_impl<D, 8, SweepCfg<17, 2, 1, 19, true>>(a, st, lc);  // helper warps: 5 5 5 | 2 edge + 2 helpers
+            case 31: return fused_impl<D, 8, SweepCfg<16, 2, 1, 18, true>>(a, st, lc);  // 5 5 4 | 2 + 2 (needs 2 x 78 resident blocks: not at KITTI width)
+            case 33: return fused_impl<D, 8, SweepCfg<18, 2, 1, 20, true>>(a, st, lc);  // 5 5 5 | 2 + 2 + 1
+            case 34: return fused_impl<D, 8, SweepCfg<17, 4, 1, 19, true>>(a, st, lc);
             default: break;
         }
     }
 #endif
     if constexpr (D <= 128) {
-        // Automatic shape: when the default would put two blocks on some SMs and one on others (rows advance in
-        // lock-step, so the crowded SMs set the pace), prefer one wide block per SM with a few SMs left over for the
-        // small kernels of the other frames in flight.  KITTI width: 2 x 66 blocks of 19 columns on 148 SMs.
-        int device = 0, sms = 0;
-        cudaGetDevice(&device);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-        using Wide = SweepCfg<19, 4, 1>;
-        using Def = typename DefaultCfg<D>::type;
-        const int wide_blocks = a.views * ((a.w + Wide::NW - 1) / Wide::NW), def_blocks = a.views * ((a.w + Def::NW - 1) / Def::NW);
-        if (def_blocks > sms && wide_blocks <= sms - 12) return fused_impl<D, 8, Wide>(a, st, lc);
+        switch (wide_shape<typename DefaultCfg<D>::type>(a.views, a.w)) {
+            case 17: return fused_impl<D, 8, Wide17>(a, st, lc);
+            case 19: return fused_impl<D, 8, Wide19>(a, st, lc);
+            default: break;
+        }
     }
     return fused_impl<D, 8, typename DefaultCfg<D>::type>(a, st, lc);
 }
@@ -889,16 +1073,19 @@ bool fused_dispatch_packed(const AggregateArgs& a0, cudaStream_t st, LaunchCount
         case 10: return fused_impl<DW, 8, SweepCfg<17, 2, 1, 19>, AR>(a, st, lc);
         case 11: return fused_impl<DW, 8, SweepCfg<19, 2, 1, 19>, AR>(a, st, lc);
         case 12: return fused_impl<DW, 8, SweepCfg<17, 2, 1, 18>, AR>(a, st, lc);
+        case 13: return fused_impl<DW, 8, SweepCfg<17, 2, 1, 19, true>, AR>(a, st, lc);
+        case 14: return fused_impl<DW, 8, SweepCfg<18, 2, 1, 20, true>, AR>(a, st, lc);
         default: break;
     }
 #endif
-    int device = 0, sms = 0;
-    cudaGetDevice(&device);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-    using Wide = SweepCfg<19, 4, 1>;
     using Def = typename DefaultCfg<DW>::type;
-    const int wide_blocks = a.views * ((a.w + Wide::NW - 1) / Wide::NW), def_blocks = a.views * ((a.w + Def::NW - 1) / Def::NW);
-    if (DW <= 128 && def_blocks > sms && wide_blocks <= sms - 12) return fused_impl<DW, 8, Wide, AR>(a, st, lc);
+    if constexpr (DW <= 128) {
+        switch (wide_shape<Def>(a.views, a.w)) {
+            case 17: return fused_impl<DW, 8, Wide17, AR>(a, st, lc);
+            case 19: return fused_impl<DW, 8, Wide19, AR>(a, st, lc);
+            default: break;
+        }
+    }
     return fused_impl<DW, 8, Def, AR>(a, st, lc);
 }
 

@@ -67,6 +67,22 @@ def test_sgm_small_and_ragged_sizes_vs_oracle(h, w, d):
     _check_sgm_against_restatement(L, R, 1, d)
 
 
+@pytest.mark.parametrize("h,w,d,integer", [
+    (18, 1250, 128, False), (17, 1255, 64, False), (16, 1258, 128, False),  # 17-column blocks: last block of 9 / 14 / 17 columns
+    (20, 760, 128, False), (18, 1243, 32, False),                          # ... of 12 / 2 columns
+    (18, 1259, 128, False), (16, 1290, 64, False),                         # too wide for 17-column blocks: 19 columns, last block 5 / 17
+    (18, 1250, 128, True), (16, 1259, 128, True), (17, 1255, 64, True),
+])
+def test_sgm_wide_rows_one_block_per_sm_shapes_vs_oracle(h, w, d, integer):
+    # widths above ~740 px switch the sweeps to one wide block per SM (sweep_kernels.cu: wide_shape); the hardware warp ->
+    # column permutation of those blocks depends on how many columns the ragged last block of a row has
+    L, R, _ = synth.random_dot_pair(h, w, seed=h * w + d, bg=3, fg=min(17, d // 2), noise=20)
+    if integer:
+        _check_sgm_against_restatement(L, R, 1, d, flags=capi.FLAG_INTEGER, box_w=1, box_h=1)
+    else:
+        _check_sgm_against_restatement(L, R, 1, d)
+
+
 def test_sgm_halo_tag_sequence_wraps(monkeypatch):
     # the cross-block exchange of the sweeps tags every vector with (launch sequence, row); the sequence wraps after 2^20
     # sweep launches (~5e5 frames), where the ring is wiped and the numbering restarts: run frames across that point
