@@ -370,6 +370,7 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
     using HIO = HaloIO<D>;
     constexpr int E = LL::E;
     constexpr bool DIAG = PATHS == 8;
+    constexpr bool TOGETHER = E <= 4;  // see the block-edge branch of the row loop
     static_assert(NW >= 2 && PF % 2 == 0, "a block needs two columns; PF must be even");
     constexpr unsigned VEC_BYTES = D * 4, WARP_BYTES = 2 * VEC_BYTES, PAR_BYTES = NW * WARP_BYTES, MIN_PAR_BYTES = NW * 2 * 4;
     const int lane = threadIdx.x & 31;
@@ -494,9 +495,11 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
                 float Gin[E];
                 const bool peek_ok = EDGE && DIAG && g_global && r > 0 && !dead && !debug_skip(a, 1);
                 bool got = false;
+                float mGin = 0.f;
                 if (peek_ok) {
                     if (early_ok) got = HIO::accept(early, Gin, tag - 1u);
                     if (!got) HIO::peek(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, peeked);
+                    else if (TOGETHER) mGin = AR::vmin(Gin);  // its warp-wide minimum: ahead of the barrier wait, off the row's critical path
                 }
                 asm volatile("cp.async.wait_group %0;" ::"n"(PF - 1) : "memory");  // this row's C / A / B have landed
                 lds_pixel<D>(rbase + u * SLOT_BYTES, C);
@@ -534,6 +537,22 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
                         lds_pixel<D>(g_src + (par ^ 1u) * PAR_BYTES, P[2]);
                         mP[2] = lds_f32(gm_src + (par ^ 1u) * MIN_PAR_BYTES);
                         AR::template step_n<3>(P, C, mP, lane, a.P1, a.P2);
+                        if (UP) select_pending(r - 1);
+                    } else if (TOGETHER && got && !debug_skip(a, 64)) {
+                        // block-edge warp whose neighbour-block vector arrived early (the usual case: blocks run in step and
+                        // the neighbour published it about a row ago): all three paths advance together, as in an interior warp
+                        // (1242x375: -2.3 % at D = 128, -2.4 % at D = 64, -4.4 % in the integer mode; with 8 values per lane,
+                        // i.e. D = 256, the three-path step spills and 1080p gets 8 % slower, hence TOGETHER)
+#pragma unroll
+                        for (int k = 0; k < E; ++k) P[2][k] = Gin[k];
+                        mP[2] = mGin;
+                        AR::template step_n<3>(P, C, mP, lane, a.P1, a.P2);
+                        if (f_init) {
+#pragma unroll
+                            for (int k = 0; k < E; ++k) P[0][k] = C[k];
+                            mP[0] = AR::vmin(C);
+                        }
+                        if (f_pub) HIO::publish(f_pub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, P[0], tag);
                         if (UP) select_pending(r - 1);
                     } else {
                         // block-edge warp: F first (a neighbouring block is waiting for it), then V and G together
@@ -985,9 +1004,7 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
         }();
         switch (cfg64) {
             case 16: return fused_impl<D, 8, SweepCfg<19, 2, 1>>(a, st, lc);
-            case 24: return fused_impl<D, 8, SweepCfg<17, 2, 1, 19>>(a, st, lc);
             case 30: return fused_impl<D, 8, SweepCfg<17, 2, 1, 19, true>>(a, st, lc);
-            case 34: return fused_impl<D, 8, SweepCfg<17, 4, 1, 19, true>>(a, st, lc);
             default: break;
         }
     }
@@ -997,39 +1014,14 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
             return e ? std::atoi(e) : 0;
         }();
         switch (cfg) {
-            case 1: return fused_impl<D, 8, SweepCfg<8, 4, 3>>(a, st, lc);
-            case 2: return fused_impl<D, 8, SweepCfg<10, 6, 2>>(a, st, lc);
-            case 3: return fused_impl<D, 8, SweepCfg<10, 2, 2>>(a, st, lc);
-            case 4: return fused_impl<D, 8, SweepCfg<12, 4, 2>>(a, st, lc);
-            case 5: return fused_impl<D, 8, SweepCfg<10, 2, 3>>(a, st, lc);
-            case 6: return fused_impl<D, 8, SweepCfg<8, 2, 4>>(a, st, lc);
-            case 7: return fused_impl<D, 8, SweepCfg<17, 4, 1>>(a, st, lc);
-            case 8: return fused_impl<D, 8, SweepCfg<17, 6, 1>>(a, st, lc);
-            case 9: return fused_impl<D, 8, SweepCfg<9, 4, 2>>(a, st, lc);
-            case 10: return fused_impl<D, 8, SweepCfg<18, 4, 1>>(a, st, lc);
-            case 11: return fused_impl<D, 8, SweepCfg<18, 6, 1>>(a, st, lc);
             case 12: return fused_impl<D, 8, SweepCfg<19, 4, 1>>(a, st, lc);
             case 13: return fused_impl<D, 8, typename DefaultCfg<D>::type>(a, st, lc);
-            case 14: return fused_impl<D, 8, SweepCfg<19, 6, 1>>(a, st, lc);
-            case 15: return fused_impl<D, 8, SweepCfg<19, 8, 1>>(a, st, lc);
             case 16: return fused_impl<D, 8, SweepCfg<19, 2, 1>>(a, st, lc);
-            case 17: return fused_impl<D, 8, SweepCfg<16, 4, 1>>(a, st, lc);
-            case 18: return fused_impl<D, 8, SweepCfg<20, 4, 1>>(a, st, lc);
-            case 19: return fused_impl<D, 8, SweepCfg<17, 4, 1, 17>>(a, st, lc);  // schedulers host 5 4 4 | 2 edge + 2
-            case 20: return fused_impl<D, 8, SweepCfg<17, 4, 1, 18>>(a, st, lc);  // 5 5 4 | 2 + 1
-            case 21: return fused_impl<D, 8, SweepCfg<17, 4, 1, 19>>(a, st, lc);  // 5 5 5 | 2
-            case 22: return fused_impl<D, 8, SweepCfg<18, 4, 1, 20>>(a, st, lc);  // 5 5 5 | 2 + 1
-            case 23: return fused_impl<D, 8, SweepCfg<17, 6, 1, 19>>(a, st, lc);
-            case 24: return fused_impl<D, 8, SweepCfg<17, 2, 1, 19>>(a, st, lc);
-            case 25: return fused_impl<D, 8, SweepCfg<18, 4, 1, 18>>(a, st, lc);  // 5 5 4 | 2 + 2
-            case 26: return fused_impl<D, 8, SweepCfg<17, 2, 1, 18>>(a, st, lc);
-            case 27: return fused_impl<D, 8, SweepCfg<17, 2, 1, 17>>(a, st, lc);
-            case 28: return fused_impl<D, 8, SweepCfg<18, 2, 1, 20>>(a, st, lc);
-            case 29: return fused_impl<D, 8, SweepCfg<18, 2, 1, 18>>(a, st, lc);
+            case 21: return fused_impl<D, 8, SweepCfg<17, 4, 1, 19>>(a, st, lc);        // schedulers host 5 5 5 | 2 edge warps
+            case 26: return fused_impl<D, 8, SweepCfg<17, 2, 1, 18>>(a, st, lc);        // 5 5 4 | 2 + 1
+            case 27: return fused_impl<D, 8, SweepCfg<17, 2, 1, 17>>(a, st, lc);        // 5 4 4 | 2 + 2
             case 30: return fused_impl<D, 8, SweepCfg<17, 2, 1, 19, true>>(a, st, lc);  // helper warps: 5 5 5 | 2 edge + 2 helpers
-            case 31: return fused_impl<D, 8, SweepCfg<16, 2, 1, 18, true>>(a, st, lc);  // 5 5 4 | 2 + 2 (needs 2 x 78 resident blocks: not at KITTI width)
             case 33: return fused_impl<D, 8, SweepCfg<18, 2, 1, 20, true>>(a, st, lc);  // 5 5 5 | 2 + 2 + 1
-            case 34: return fused_impl<D, 8, SweepCfg<17, 4, 1, 19, true>>(a, st, lc);
             default: break;
         }
     }
@@ -1062,19 +1054,9 @@ bool fused_dispatch_packed(const AggregateArgs& a0, cudaStream_t st, LaunchCount
     }();
     switch (cfg) {
         case 1: return fused_impl<DW, 8, SweepCfg<10, 4, 2>, AR>(a, st, lc);
-        case 2: return fused_impl<DW, 8, SweepCfg<8, 4, 3>, AR>(a, st, lc);
         case 3: return fused_impl<DW, 8, SweepCfg<19, 4, 1>, AR>(a, st, lc);
-        case 4: return fused_impl<DW, 8, SweepCfg<19, 6, 1>, AR>(a, st, lc);
-        case 5: return fused_impl<DW, 8, SweepCfg<17, 4, 1>, AR>(a, st, lc);
-        case 6: return fused_impl<DW, 8, SweepCfg<9, 4, 2>, AR>(a, st, lc);
-        case 7: return fused_impl<DW, 8, SweepCfg<17, 4, 1, 19>, AR>(a, st, lc);
-        case 8: return fused_impl<DW, 8, SweepCfg<18, 4, 1, 20>, AR>(a, st, lc);
-        case 9: return fused_impl<DW, 8, SweepCfg<17, 4, 1, 18>, AR>(a, st, lc);
-        case 10: return fused_impl<DW, 8, SweepCfg<17, 2, 1, 19>, AR>(a, st, lc);
         case 11: return fused_impl<DW, 8, SweepCfg<19, 2, 1, 19>, AR>(a, st, lc);
-        case 12: return fused_impl<DW, 8, SweepCfg<17, 2, 1, 18>, AR>(a, st, lc);
         case 13: return fused_impl<DW, 8, SweepCfg<17, 2, 1, 19, true>, AR>(a, st, lc);
-        case 14: return fused_impl<DW, 8, SweepCfg<18, 2, 1, 20, true>, AR>(a, st, lc);
         default: break;
     }
 #endif
