@@ -24,6 +24,7 @@
 // leave every operation on the values to a policy class AR (sgm_device.cuh): F32Arith<D> is the reference's float32
 // arithmetic (one word = one cost), S16x2Arith<D/2> the integer / DPX mode (one word = two 16-bit costs, SGM_FLAG_INTEGER).
 // The template parameter D of a kernel is the number of WORDS per pixel.
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -481,6 +482,7 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
     // next row, where a miss falls back to a second look and then to polling
     unsigned long long early[E];
     bool early_ok = false;
+    int n_early = 0, n_peek = 0, n_poll = 0;  // (tuning build, bit 128: where the neighbour block's vector was found, printed per warp)
     for (int r0 = 0; r0 < h; r0 += PF) {
 #pragma unroll
         for (int u = 0; u < PF; ++u) {
@@ -498,6 +500,7 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
                 float mGin = 0.f;
                 if (peek_ok) {
                     if (early_ok) got = HIO::accept(early, Gin, tag - 1u);
+                    n_early += got;
                     if (!got) HIO::peek(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, peeked);
                     else if (TOGETHER) mGin = AR::vmin(Gin);  // its warp-wide minimum: ahead of the barrier wait, off the row's critical path
                 }
@@ -568,10 +571,14 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
                         if (f_pub) HIO::publish(f_pub + (size_t)(r % HALO_RING) * HIO::SLOT_WORDS, lane, P0[0], tag);
                         if (UP) select_pending(r - 1);  // the neighbour's vector may still be on its way: use the time
                         float P12[2][E], m12[2];
-                        if (peek_ok && !got && !HIO::accept(peeked, Gin, tag - 1u) &&
-                            !HIO::consume(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, Gin, tag - 1u)) {
-                            dead = true;
-                            if (lane == 0) atomicExch(a.error, 1);
+                        if (peek_ok && !got) {
+                            const bool second = HIO::accept(peeked, Gin, tag - 1u);
+                            n_peek += second;
+                            n_poll += !second;
+                            if (!second && !HIO::consume(g_sub + (size_t)((r - 1) % HALO_RING) * HIO::SLOT_WORDS, lane, Gin, tag - 1u)) {
+                                dead = true;
+                                if (lane == 0) atomicExch(a.error, 1);
+                            }
                         }
 #pragma unroll
                         for (int k = 0; k < E; ++k) P12[1][k] = Gin[k];
@@ -676,6 +683,9 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
             }
         }
     }
+    if (EDGE && debug_skip(a, 128) && g_global && lane == 0 && (blk == 1 || blk == nblk / 2) && blockIdx.y == 0)
+        printf("sweep %s blk %d col %d: neighbour vector found early %d, at the second look %d, by polling %d\n", UP ? "up" : "down", blk, wid,
+               n_early, n_peek, n_poll);
     if (UP && !no_out) {  // drain the pipeline: the last row's selection and the rows still stashed
         select_pending(h - 1);
         flush_rows(h - 1);
