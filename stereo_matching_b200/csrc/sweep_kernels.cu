@@ -341,7 +341,7 @@ template <int NW, int HWW, bool HELP>
 __device__ __forceinline__ int sweep_column_of_warp(int hw, int nact, bool identity) {
     static_assert(HWW >= NW + (HELP ? 2 : 0), "one hardware warp per column (and helper) at least");
     static_assert(!HELP || NW >= 16, "helper warps sit on hardware warps 11 and 15");
-    if (identity || nact < 9 || NW < 16) return hw < nact ? hw : -1;
+    if (identity || nact < 9 || NW < 13) return hw < nact ? hw : -1;  // (the 8- and 10-column default shapes keep the natural order)
     if (hw == 3) return 0;
     if (hw == 7) return nact - 1;
     if (HELP && hw == 11) return NW;
@@ -814,15 +814,23 @@ __device__ __forceinline__ void sweep_helper_body(const SweepArgs& a, const floa
     if (UP && ((h - 1) & 31) != 31) flush_rows(h - 1);
 }
 
+// floats of the diagonal exchange buffer at the start of the dynamic shared memory (53 KB for 13 columns at D = 256: more than
+// static shared memory may hold)
+template <int D, int NW, int PATHS>
+__host__ __device__ constexpr int sweep_xch_floats() {
+    return PATHS == 8 ? 2 * NW * 2 * D : 0;
+}
+
 template <int D, int NW, int MODE, int PATHS, int PF, int MINB, class AR, int HWW = NW, bool HELP = false>
 __global__ void __launch_bounds__(HWW * 32, MINB) sgm_sweep_kernel(const SweepArgs a) {
     constexpr bool DIAG = PATHS == 8;
     static_assert(!HELP || DIAG, "helper warps exist for the 8-path sweeps only");
-    __shared__ __align__(16) float xch[DIAG ? 2 * NW * 2 * D : 4];  // [parity][warp][0 = Pl, 1 = Pr][d]
     __shared__ float xmin[DIAG ? 2 * NW * 2 : 1];                   // [parity][warp][0 = Pl, 1 = Pr] min of the vector
     __shared__ __align__(16) float vx[HELP ? 2 * 2 * D : 4];        // [parity][edge column][d]: vertical path, for the helper warps
     __shared__ __align__(8) unsigned long long bar_mem;
-    extern __shared__ __align__(16) float sring[];  // [NW (+ 2 helpers)][PF][3][D]
+    extern __shared__ __align__(16) float dyn_smem[];
+    float* xch = dyn_smem;                                 // [parity][warp][0 = Pl, 1 = Pr][d] (8 paths only)
+    float* sring = dyn_smem + sweep_xch_floats<D, NW, PATHS>();  // [NW (+ 2 helpers)][PF][3][D]
     const int blk = blockIdx.x;
     const int nact = min(NW, a.w - blk * NW);  // columns (= warps) of this block that exist
     const bool helpers = sweep_block_has_helpers<HELP>(nact, debug_skip(a, 16));
@@ -859,15 +867,15 @@ struct SweepCfg {
     static constexpr bool HELP = HELP_;  // two of the spare warps do the output work of the block-edge columns (8 paths)
 };
 
-template <int D, class CFG>
-constexpr size_t sweep_ring_bytes() {
-    return (size_t)(CFG::NW + (CFG::HELP ? 2 : 0)) * CFG::PF * 3 * D * sizeof(float);
+template <int D, class CFG, int PATHS>
+constexpr size_t sweep_smem_bytes() {  // dynamic shared memory of a sweep block: exchange buffer + the warps' rings
+    return ((size_t)sweep_xch_floats<D, CFG::NW, PATHS>() + (size_t)(CFG::NW + (CFG::HELP ? 2 : 0)) * CFG::PF * 3 * D) * sizeof(float);
 }
 
 template <int D, int MODE, int PATHS, class CFG, class AR>
 cudaError_t launch_sweep(const SweepArgs& sa, int nblk, int views, bool cooperative, cudaStream_t st) {
     auto kern = sgm_sweep_kernel<D, CFG::NW, MODE, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW, CFG::HELP>;
-    constexpr size_t ring_bytes = sweep_ring_bytes<D, CFG>();
+    constexpr size_t ring_bytes = sweep_smem_bytes<D, CFG, PATHS>();
     cudaError_t attr = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ring_bytes);  // per device: cheap, so always
     if (attr != cudaSuccess) return attr;
     if (!cooperative) {
@@ -887,8 +895,8 @@ int sweep_capacity(int device) {
     cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device);
     // the ring may exceed the default 48 KB of dynamic shared memory: opt in before asking for the occupancy
     auto ask = [&](auto kern, int& out) {
-        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_ring_bytes<D, CFG>());
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&out, kern, CFG::HWW * 32, sweep_ring_bytes<D, CFG>());
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sweep_smem_bytes<D, CFG, PATHS>());
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&out, kern, CFG::HWW * 32, sweep_smem_bytes<D, CFG, PATHS>());
     };
     ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_DOWN, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW, CFG::HELP>, per_sm[0]);
     ask(sgm_sweep_kernel<D, CFG::NW, SWEEP_UP, PATHS, CFG::PF, CFG::MINB, AR, CFG::HWW, CFG::HELP>, per_sm[1]);
@@ -981,32 +989,55 @@ struct DefaultCfg<128> {
     using type = SweepCfg<10, 4, 2>;  // 1242x375: 250 blocks of 10 columns, 2 per SM
 };
 
-// Automatic shape for up to 128 words per pixel: when the default would put two blocks on some SMs and one on others (rows
-// advance in lock-step, so the crowded SMs set the pace), prefer ONE wide block per SM.  Both wide shapes run 19 hardware
-// warps (more would put six warps on one scheduler's register file: 80 registers instead of 96, heavy spills) and keep two
-// rows in flight per warp (four cost more spill traffic in the up sweep than they hide latency).
-//   Wide17: 17 columns; the two block-edge warps have a warp scheduler to themselves (sweep_column_of_warp).
-//           KITTI width: 2 x 74 blocks = one per SM of a B200.  1242x375 D=128: aggregation 1.14 ms.
-//   Wide19: 19 columns, for widths whose 17-column grid does not fit the device (edge warps share their scheduler with two
-//           interior warps; 1242x375 D=128: 1.20 ms).
+// Automatic launch shape.  Rows advance in lock-step, so the time of a frame's sweep goes with
+//     (launches: 1, or 2 when both views do not fit a resident grid) x (columns on the most crowded SM).
+// The default shapes (8 or 10 columns, 2 - 3 blocks per SM) are right for narrow images; when they would stack blocks on
+// some SMs, ONE wide block per SM is better:
+//   Wide17: 17 columns on 19 hardware warps; the two block-edge warps have a warp scheduler to themselves
+//           (sweep_column_of_warp).  KITTI width: 2 x 74 blocks = one per SM of a B200.  1242x375 D=128: 1.22 -> 1.12 ms.
+//   Wide19: 19 columns, for widths whose 17-column grid does not fit the device (the edge warps share their scheduler with
+//           two interior warps; 1242x375 D=128: 1.20 ms).
+//   Wide13: 13 columns on 15 hardware warps: 1920 columns = 148 blocks, one view per launch.  The only wide shape for 8
+//           values per lane (D = 256): up to 16 warps a block may use 128 registers, with 17 - 20 only 96 (five warps on one
+//           scheduler's 16 K registers), which that body does not fit.
+// All of them keep two rows in flight per warp (four cost more spill traffic in the up sweep than they hide latency); 21
+// hardware warps would cap the kernels at 80 registers (1242x375 D=128: 1.25 ms).
+using Wide13 = SweepCfg<13, 2, 1, 15>;
 using Wide17 = SweepCfg<17, 2, 1, 19>;
 using Wide19 = SweepCfg<19, 2, 1, 19>;
-template <class Def>
+template <class Def, bool UP_TO_4_PER_LANE>
 int wide_shape(int views, int w) {
     int device = 0, sms = 0;
     cudaGetDevice(&device);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-    const int def_blocks = views * ((w + Def::NW - 1) / Def::NW);
-    if (def_blocks <= sms) return 0;  // the default shape already has at most one block per SM
-    if (views * ((w + Wide17::NW - 1) / Wide17::NW) <= sms) return 17;
-    if (views * ((w + Wide19::NW - 1) / Wide19::NW) <= sms - 12) return 19;
-    return 0;
+    auto cost = [&](int nw, int per_sm) {  // 0: the grid cannot be resident
+        const int nblk = (w + nw - 1) / nw, cap = sms * per_sm;
+        if (nblk > cap) return 0;
+        const int launches = views * nblk > cap ? views : 1;
+        const int per_launch = launches == 1 ? views * nblk : nblk;
+        return launches * nw * ((per_launch + sms - 1) / sms);
+    };
+    int best = 0, best_cost = cost(Def::NW, Def::MINB);
+    const int candidates[3] = {17, 19, 13};
+    for (int nw : candidates) {
+        if (!UP_TO_4_PER_LANE && nw != 13) continue;
+        const int c = cost(nw, 1);
+        if (c && (!best_cost || c < best_cost)) {
+            best = nw;
+            best_cost = c;
+        }
+    }
+    return best;
 }
 
 template <int D>
 bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
     if (a.paths != 8) return fused_impl<D, 4, typename DefaultCfg<D>::type>(a, st, lc);
 #ifdef SGM_B200_TUNING
+    if constexpr (D == 256) {
+        static const bool def256 = std::getenv("SGM_B200_SWEEP_CFG") && std::atoi(std::getenv("SGM_B200_SWEEP_CFG")) == 13;
+        if (def256) return fused_impl<D, 8, typename DefaultCfg<D>::type>(a, st, lc);
+    }
     if constexpr (D == 64) {  // a short list for D = 64 (every entry costs three kernels of compile time)
         static const int cfg64 = [] {
             const char* e = std::getenv("SGM_B200_SWEEP_CFG");
@@ -1036,10 +1067,16 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
         }
     }
 #endif
-    if constexpr (D <= 128) {
-        switch (wide_shape<typename DefaultCfg<D>::type>(a.views, a.w)) {
-            case 17: return fused_impl<D, 8, Wide17>(a, st, lc);
-            case 19: return fused_impl<D, 8, Wide19>(a, st, lc);
+    constexpr bool NARROW = LaneLayout<D>::E <= 4;
+    if constexpr (LaneLayout<D>::E <= 8) {
+        switch (wide_shape<typename DefaultCfg<D>::type, NARROW>(a.views, a.w)) {
+            case 13: return fused_impl<D, 8, Wide13>(a, st, lc);
+            case 17:
+                if constexpr (NARROW) return fused_impl<D, 8, Wide17>(a, st, lc);
+                break;
+            case 19:
+                if constexpr (NARROW) return fused_impl<D, 8, Wide19>(a, st, lc);
+                break;
             default: break;
         }
     }
@@ -1071,10 +1108,16 @@ bool fused_dispatch_packed(const AggregateArgs& a0, cudaStream_t st, LaunchCount
     }
 #endif
     using Def = typename DefaultCfg<DW>::type;
-    if constexpr (DW <= 128) {
-        switch (wide_shape<Def>(a.views, a.w)) {
-            case 17: return fused_impl<DW, 8, Wide17, AR>(a, st, lc);
-            case 19: return fused_impl<DW, 8, Wide19, AR>(a, st, lc);
+    constexpr bool NARROW = LaneLayout<DW>::E <= 4;
+    if constexpr (LaneLayout<DW>::E <= 8) {
+        switch (wide_shape<Def, NARROW>(a.views, a.w)) {
+            case 13: return fused_impl<DW, 8, Wide13, AR>(a, st, lc);
+            case 17:
+                if constexpr (NARROW) return fused_impl<DW, 8, Wide17, AR>(a, st, lc);
+                break;
+            case 19:
+                if constexpr (NARROW) return fused_impl<DW, 8, Wide19, AR>(a, st, lc);
+                break;
             default: break;
         }
     }

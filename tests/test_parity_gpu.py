@@ -72,10 +72,12 @@ def test_sgm_small_and_ragged_sizes_vs_oracle(h, w, d):
     (20, 760, 128, False), (18, 1243, 32, False),                          # ... of 12 / 2 columns
     (18, 1259, 128, False), (16, 1290, 64, False),                         # too wide for 17-column blocks: 19 columns, last block 5 / 17
     (18, 1250, 128, True), (16, 1259, 128, True), (17, 1255, 64, True),
+    (16, 1920, 256, False), (16, 1500, 256, False),                        # 13-column blocks, one view per launch: last block 9 / 5
+    (16, 1910, 256, True), (18, 1500, 128, False),
 ])
 def test_sgm_wide_rows_one_block_per_sm_shapes_vs_oracle(h, w, d, integer):
-    # widths above ~740 px switch the sweeps to one wide block per SM (sweep_kernels.cu: wide_shape); the hardware warp ->
-    # column permutation of those blocks depends on how many columns the ragged last block of a row has
+    # wide images switch the sweeps to one wide block per SM (sweep_kernels.cu: wide_shape picks 13, 17 or 19 columns); the
+    # hardware warp -> column permutation of those blocks depends on how many columns the ragged last block of a row has
     L, R, _ = synth.random_dot_pair(h, w, seed=h * w + d, bg=3, fg=min(17, d // 2), noise=20)
     if integer:
         _check_sgm_against_restatement(L, R, 1, d, flags=capi.FLAG_INTEGER, box_w=1, box_h=1)
