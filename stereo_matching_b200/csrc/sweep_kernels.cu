@@ -957,6 +957,13 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
     sa.min_gap = a.min_gap;
     sa.vol_stride = vol;
     sa.img_stride = (size_t)a.h * a.w;
+    bool cooperative = PATHS == 8;
+#ifdef SGM_B200_TUNING
+    // experiment: plain launches (blocks start as SMs free up instead of all at once).  NOT safe with several frames in flight:
+    // two half-resident sweep grids wait for each other until the time-out.
+    static const bool plain = std::getenv("SGM_B200_SWEEP_PLAIN_LAUNCH") != nullptr;
+    if (plain) cooperative = false;
+#endif
     for (int up = 0; up < 2; ++up) {
         // every sweep launch gets its own tag range; after 2^20 launches the ring is wiped and the sequence restarts
         if (*a.launch_seq >= (1u << 20) - 1u) {
@@ -966,9 +973,9 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
         sa.tag_base = ++(*a.launch_seq) << 12;
         for (int v0 = 0; v0 < a.views; v0 += views_per_launch) {
             sa.view0 = v0;
-            cudaError_t e = !up         ? launch_sweep<D, SWEEP_DOWN, PATHS, CFG, AR>(sa, nblk, views_per_launch, PATHS == 8, st)
-                            : a.pathsum ? launch_sweep<D, SWEEP_UP_KEEP, PATHS, CFG, AR>(sa, nblk, views_per_launch, PATHS == 8, st)
-                                        : launch_sweep<D, SWEEP_UP, PATHS, CFG, AR>(sa, nblk, views_per_launch, PATHS == 8, st);
+            cudaError_t e = !up         ? launch_sweep<D, SWEEP_DOWN, PATHS, CFG, AR>(sa, nblk, views_per_launch, cooperative, st)
+                            : a.pathsum ? launch_sweep<D, SWEEP_UP_KEEP, PATHS, CFG, AR>(sa, nblk, views_per_launch, cooperative, st)
+                                        : launch_sweep<D, SWEEP_UP, PATHS, CFG, AR>(sa, nblk, views_per_launch, cooperative, st);
             if (e != cudaSuccess && lc.err == cudaSuccess) {
                 lc.err = e;
                 lc.failed = "sgm_sweep_kernel (launch)";

@@ -1,5 +1,6 @@
-"""Small frames through every kernel, for `compute-sanitizer --tool memcheck|racecheck python tests/sanitize_small.py`
-(dev helper, not a pytest; one tool per GPU call, see B200_PROFILING.md)."""
+"""Small frames through every kernel, written for `compute-sanitizer --tool memcheck|racecheck python tests/sanitize_small.py`
+(dev helper, not a pytest; one tool per GPU call, see B200_PROFILING.md).  compute-sanitizer was closed on the GPU pool during
+round 2 (profiles/r02_summary.md), so the script only serves as a quick run of every kernel on small and on wide frames."""
 import os
 import sys
 

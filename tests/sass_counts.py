@@ -32,7 +32,8 @@ for ln in sass.splitlines():
 total = collections.Counter()
 print(f"# SASS mnemonic counts per kernel of {os.path.relpath(lib, ROOT)} (cuobjdump -sass; sm_100a).  Columns: only non-zero counts.")
 for name, c in per.items():
-    short = re.sub(r"\(.*", "", demangle(name)).replace("sgmb200::(anonymous namespace)::", "").replace("void ", "")
+    short = demangle(name).replace("(anonymous namespace)::", "").replace("sgmb200::", "").replace("void ", "")
+    short = re.sub(r">\(.*", ">", short) if ">(" in short else re.sub(r"\(.*", "", short)  # drop the parameter list, keep template arguments
     items = " ".join(f"{k}={v}" for k, v in sorted(c.items()) if k != "_total" and v)
     print(f"{short[:110]:<110} instr={c['_total']:<6} {items}")
     total.update(c)
