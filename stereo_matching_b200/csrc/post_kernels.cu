@@ -116,6 +116,7 @@ __global__ void __launch_bounds__(512) median_solve_kernel(float* f, const unsig
                                                             int h, int w, int d) {
     using MW = MedianWin<WH, WW>;
     constexpr int NB = MW::NB, NC = MW::NC, HALF = MW::NWIN / 2;
+    static_assert(NB <= 32, "one lane per window entry");
     extern __shared__ __align__(16) unsigned char msm[];
     constexpr int NBP = NB + 2;  // row pitch: NB window entries + the reference mask + pad = an odd number of 32-bit words (no bank collisions between rows)
     unsigned short* win = reinterpret_cast<unsigned short*>(msm);            // [CHUNK][NBP]
@@ -289,7 +290,11 @@ __global__ void __launch_bounds__(512) median_solve_kernel(float* f, const unsig
         // warp, round-robin 158 k / 1.10 M; the same after peeling the never-fillable candidates to a fixpoint in parallel
         // rounds (75 k / 116 k for the peeling) 145 k / 1.17 M; ONE warp walking the survivors in order 481 k / 1.76 M.
         // They all end up near (number of filled holes) x (400 - 1000 cycles): consecutive holes are neighbours, so the
-        // medians form one long chain, and a median costs a dozen warp-wide votes / reductions at 20 - 40 cycles each.
+        // medians form one long chain.  Later: the median by rank counting instead of bisection (below) 166 k / 1.29 M; with it,
+        // looking only at the LATEST open reference per round plus forwarding a fill to the next lane in registers 497 k / 1.30 M
+        // (the never-fillable candidates of an SGM frame are then found in chain order instead of at once); all open references
+        // looked at with independent, predicated loads instead of a loop over the set bits (shipped) 112 k / 1.02 M: on a
+        // block-matching frame the chain runs DOWN the invalid left band, 3 - 5 dependent fills per image row, one round each.
         volatile unsigned short* vval = val;
         for (int g = wid; g * 32 < cn; g += nwarp) {
             const int c = g * 32 + lane;
@@ -297,15 +302,28 @@ __global__ void __launch_bounds__(512) median_solve_kernel(float* f, const unsig
             const unsigned short* wc = win + (size_t)(unresolved ? c : 0) * NBP;
             unsigned refmask = wc[NB];             // references still unresolved
             int known = litv[unresolved ? c : 0];  // valid entries seen so far: literals + references resolved to a value
+            // the candidate's causal references, fetched once (entries that are literals are never used as an index)
+            int ref[NC];
+#pragma unroll
+            for (int t = 0; t < NC; ++t) ref[t] = wc[t] & 0x7fffu;
             for (;;) {
                 bool ready = false, progress = false;
                 if (unresolved) {
-                    for (unsigned m = refmask; m; m &= m - 1) {
-                        const int t = __ffs(m) - 1;
-                        const unsigned short x = vval[wc[t] & 0x7fffu];
-                        if (x != MED_UNRESOLVED) {  // a resolved reference is looked at once
+                    // look at every open reference: NC independent, predicated look-ups issued together.  (A loop over the set
+                    // bits of refmask — find the bit, load the entry, load the value, branch — costs its full latency per
+                    // open reference, ~1000 cycles per round for a hole in the middle of a band of holes.)
+                    constexpr unsigned OPEN = 0xffffu;  // == MED_UNRESOLVED
+                    unsigned xs[NC];
+#pragma unroll
+                    for (int t = 0; t < NC; ++t) {
+                        xs[t] = OPEN;
+                        if ((refmask >> t) & 1u) xs[t] = vval[ref[t]];
+                    }
+#pragma unroll
+                    for (int t = 0; t < NC; ++t) {
+                        if (xs[t] != OPEN) {  // (only open references were looked at) a resolved reference is consumed once
                             refmask &= ~(1u << t);
-                            known += x != MED_INVALID ? 1 : 0;
+                            known += xs[t] != 0x7fffu ? 1 : 0;  // MED_INVALID
                             progress = true;
                         }
                     }
@@ -318,7 +336,7 @@ __global__ void __launch_bounds__(512) median_solve_kernel(float* f, const unsig
                     }
                 }
                 // ready candidates are evaluated by the whole warp, one after the other: lane t holds window entry t, the
-                // median sorted[cnt / 2] = the smallest value with at least cnt / 2 + 1 entries <= it, by bisection on ballots
+                // median is the entry at position cnt / 2 of the sorted valid entries
                 for (unsigned todo = __ballot_sync(FULL_MASK, ready); todo; todo &= todo - 1) {
                     const int src = __ffs(todo) - 1, cs = g * 32 + src;
                     int x = MED_INVALID;
@@ -328,27 +346,26 @@ __global__ void __launch_bounds__(512) median_solve_kernel(float* f, const unsig
                     }
                     const bool ok = x != MED_INVALID;
                     const int cnt = __popc(__ballot_sync(FULL_MASK, ok));
-                    int lo = __reduce_min_sync(FULL_MASK, x);              // invalid entries are 0x7fff: they sort last
-                    int hi = __reduce_max_sync(FULL_MASK, ok ? x : 0);
-                    const int need = cnt / 2 + 1;
-                    while (lo < hi) {
-                        const int mid = (lo + hi) >> 1;
-                        const int le = __popc(__ballot_sync(FULL_MASK, x <= mid));
-                        if (le >= need)
-                            hi = mid;
-                        else
-                            lo = mid + 1;
-                    }
+                    // rank by counting: (value, lane) keys are distinct, so the valid entries get the ranks 0 .. cnt-1 of the
+                    // sorted order; NB independent shuffles instead of a bisection of ~8 dependent ballot / popcount rounds
+                    // (166 k / 1.29 M cycles against 177 k / 1.35 M: the evaluation itself is not what the chain costs)
+                    const int key = ok ? ((x << 5) | lane) : 0x7fffffff;
+                    int rank = 0;
+#pragma unroll
+                    for (int t = 0; t < NB; ++t) rank += (__shfl_sync(FULL_MASK, key, t) < key) ? 1 : 0;
+                    const unsigned hit = __ballot_sync(FULL_MASK, ok && rank == cnt / 2);  // exactly one lane: cnt > HALF >= 1
+                    const int med = __shfl_sync(FULL_MASK, x, __ffs(hit) - 1);
                     if (lane == src) {
-                        vval[cs] = (unsigned short)lo;
+                        vval[cs] = (unsigned short)med;
                         unresolved = false;
                     }
                     progress = true;
                 }
                 __syncwarp();
                 if (__ballot_sync(FULL_MASK, unresolved) == 0) break;
-                // nothing moved: the group waits for an earlier group; leave the issue slots to the warps that can work
-                if (__ballot_sync(FULL_MASK, progress) == 0) __nanosleep(100);
+                // (nothing moved: the group waits for an earlier group.  A __nanosleep(100) here, meant to leave the issue slots to
+                // the warps that can work, was measured 2 - 7 % slower on the post stage than simply looking again.)
+                (void)progress;
             }
         }
         __syncthreads();
