@@ -113,7 +113,7 @@ constexpr unsigned short MED_INVALID = 0x7fff, MED_UNRESOLVED = 0xffff;
 
 template <int WH, int WW, int CHUNK>
 __global__ void __launch_bounds__(512) median_solve_kernel(float* f, const unsigned* __restrict__ bitmap, int* wordoff, int* rowoff, int* list,
-                                                            int h, int w, int d) {
+                                                            int h, int w, int d, unsigned nap_ns) {
     using MW = MedianWin<WH, WW>;
     constexpr int NB = MW::NB, NC = MW::NC, HALF = MW::NWIN / 2;
     static_assert(NB <= 32, "one lane per window entry");
@@ -363,9 +363,10 @@ __global__ void __launch_bounds__(512) median_solve_kernel(float* f, const unsig
                 }
                 __syncwarp();
                 if (__ballot_sync(FULL_MASK, unresolved) == 0) break;
-                // (nothing moved: the group waits for an earlier group.  A __nanosleep(100) here, meant to leave the issue slots to
-                // the warps that can work, was measured 2 - 7 % slower on the post stage than simply looking again.)
-                (void)progress;
+                // nothing moved: the group waits for an earlier group.  A nap here (nap_ns = 100, tuning build knob
+                // SGM_B200_MEDIAN_NAP) costs this kernel 2 - 7 % when it runs alone and changes nothing for the frames in flight
+                // beside it (bench.py with 0 / 100 on one box: 669 / 668 frames/s, block matching 2087 / 2056), so the product naps 0.
+                if (nap_ns && __ballot_sync(FULL_MASK, progress) == 0) __nanosleep(nap_ns);
             }
         }
         __syncthreads();
@@ -508,7 +509,14 @@ static void launch_lr_median_impl(const float* left, const float* right, float* 
     constexpr size_t smem = (size_t)CHUNK * ((MedianWin<WH, WW>::NB + 2) * 2 + 2 + 1);
     auto kern = median_solve_kernel<WH, WW, CHUNK>;
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    kern<<<1, 512, smem, st>>>(out_med, bitmap, wordoff, rowoff, scratch_b, h, w, d);
+    unsigned nap_ns = 0;
+#ifdef SGM_B200_TUNING
+    {
+        static const int nap = [] { const char* e = std::getenv("SGM_B200_MEDIAN_NAP"); return e ? std::atoi(e) : 0; }();
+        nap_ns = (unsigned)nap;
+    }
+#endif
+    kern<<<1, 512, smem, st>>>(out_med, bitmap, wordoff, rowoff, scratch_b, h, w, d, nap_ns);
     lc.note("median_solve_kernel");
 }
 
