@@ -18,7 +18,8 @@
 // whose payload carries its own row tag (HaloIO below: no flags, no fences).  A block only ever waits for its two
 // neighbours' PREVIOUS row, so all blocks advance within one row of their neighbours; the kernel is launched
 // cooperatively so that every block is resident, and every wait has a time-out that raises an error flag instead of
-// hanging.
+// hanging.  Launch shapes (columns per block, hardware warps, which warp scheduler the block-edge columns issue on):
+// wide_shape() / sweep_column_of_warp() below.
 //
 // The kernels are written once for both arithmetics: they move a pixel's vector as 32-bit words (`float` registers) and
 // leave every operation on the values to a policy class AR (sgm_device.cuh): F32Arith<D> is the reference's float32
