@@ -516,6 +516,22 @@ static void launch_lr_median_impl(const float* left, const float* right, float* 
         nap_ns = (unsigned)nap;
     }
 #endif
+#ifdef SGM_B200_TUNING
+    {
+        // experiment: a block small enough (threads x registers, shared memory) to sit on an SM beside a sweep block of another
+        // frame in flight, so that a 148-block cooperative sweep never waits for the SM the median is on
+        static const int small = [] { const char* e = std::getenv("SGM_B200_MEDIAN_SMALL"); return e ? std::atoi(e) : 0; }();
+        if (small > 0) {
+            constexpr int SCHUNK = 1024;
+            constexpr size_t ssmem = (size_t)SCHUNK * ((MedianWin<WH, WW>::NB + 2) * 2 + 2 + 1);
+            auto skern = median_solve_kernel<WH, WW, SCHUNK>;
+            cudaFuncSetAttribute(skern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssmem);
+            skern<<<1, small, ssmem, st>>>(out_med, bitmap, wordoff, rowoff, scratch_b, h, w, d, nap_ns);
+            lc.note("median_solve_kernel");
+            return;
+        }
+    }
+#endif
     kern<<<1, 512, smem, st>>>(out_med, bitmap, wordoff, rowoff, scratch_b, h, w, d, nap_ns);
     lc.note("median_solve_kernel");
 }

@@ -47,6 +47,7 @@ struct SweepArgs {
     uint16_t* disp;
     float* subpixel;
     float* halo;     // [views][nblk][2][HALO_RING] tagged vectors (HaloIO)
+    int cols;        // columns per block; the LAST block of a row takes what is left (at most the kernel's NW, see fused_impl)
     unsigned tag_base;  // launch sequence number << 12: tags of this launch are tag_base + row + 1
     int* error;      // set to 1 when a halo wait timed out
     int debug;       // perf experiments only (SGM_B200_SWEEP_DEBUG): 1 = skip halo waits, 2 = skip row barrier waits (WRONG results)
@@ -358,6 +359,12 @@ __device__ __forceinline__ bool sweep_block_has_helpers(int nact, bool identity)
     return HELP && !identity && nact >= 9;
 }
 
+// Columns of block blk: a.cols, except that the last block of a row takes the rest (fused_impl folds a short remainder into it
+// instead of launching a block of one or two columns that would occupy an SM of its own).
+__device__ __forceinline__ int sweep_block_columns(const SweepArgs& a, int blk, int nblk) {
+    return blk + 1 < nblk ? a.cols : a.w - blk * a.cols;
+}
+
 // EDGE (compile-time copy of a warp-uniform fact): false = an interior warp — both diagonals come from shared memory and
 // neither restarts at an image border; such a warp carries none of the halo / border code (in the generic body those
 // ~35 instructions per pixel were issued predicated-off by 17 of 19 warps).  true = a block-edge or image-border warp.
@@ -379,8 +386,8 @@ __device__ __forceinline__ void sweep_body(const SweepArgs& a, float* xch, float
     const int blk = blockIdx.x, nblk = gridDim.x;
     const int view = a.view0 + blockIdx.y;
     const int h = a.h, w = a.w;
-    const int nact = min(NW, w - blk * NW);  // columns (= warps) of this block that exist
-    const int j = blk * NW + wid;             // "wid" is the COLUMN of the block this warp works on (sweep_column_of_warp)
+    const int nact = sweep_block_columns(a, blk, nblk);  // columns (= warps) of this block
+    const int j = blk * a.cols + wid;                    // "wid" is the COLUMN of the block this warp works on (sweep_column_of_warp)
 
     // ---- roles of the two diagonals of this warp ----
     const bool swap = EDGE && DIAG && wid == 0 && blk > 0;  // F = Pr (the left block waits for it), G = Pl (comes from the left block)
@@ -712,7 +719,7 @@ __device__ __forceinline__ void sweep_helper_body(const SweepArgs& a, const floa
     const int view = a.view0 + blockIdx.y;
     const int h = a.h, w = a.w;
     const int col = which ? nact - 1 : 0;
-    const int j = blk * NW + col;
+    const int j = blk * a.cols + col;
     const bool swap = col == 0 && blk > 0;  // as in sweep_body: slot 0 / 1 of the column hold F / G = Pr / Pl instead of Pl / Pr
     const int f_id = swap ? 1 : 0, g_id = swap ? 0 : 1;
     const unsigned lane_off = lane * LL::CW * 4;
@@ -833,7 +840,7 @@ __global__ void __launch_bounds__(HWW * 32, MINB) sgm_sweep_kernel(const SweepAr
     float* xch = dyn_smem;                                 // [parity][warp][0 = Pl, 1 = Pr][d] (8 paths only)
     float* sring = dyn_smem + sweep_xch_floats<D, NW, PATHS>();  // [NW (+ 2 helpers)][PF][3][D]
     const int blk = blockIdx.x;
-    const int nact = min(NW, a.w - blk * NW);  // columns (= warps) of this block that exist
+    const int nact = sweep_block_columns(a, blk, gridDim.x);  // columns (= warps) of this block
     const bool helpers = sweep_block_has_helpers<HELP>(nact, debug_skip(a, 16));
     const unsigned bar = smem_u32(&bar_mem);
     if (DIAG) {
@@ -848,7 +855,7 @@ __global__ void __launch_bounds__(HWW * 32, MINB) sgm_sweep_kernel(const SweepAr
             return;
         }
     }
-    const int j = blk * NW + wid;
+    const int j = blk * a.cols + wid;
     // block-edge warps (they exchange with a neighbouring block) and image-border columns take the general body
     const bool edge = DIAG && (wid == 0 || wid == nact - 1 || j == 0 || j == a.w - 1);
     if (HELP && edge && helpers)
@@ -887,6 +894,13 @@ cudaError_t launch_sweep(const SweepArgs& sa, int nblk, int views, bool cooperat
     return cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kern), dim3(nblk, views), dim3(CFG::HWW * 32), params, ring_bytes, st);
 }
 
+// blocks per image row for `cols` columns per block in a kernel that can take `capacity` columns (see fused_impl)
+inline int sweep_blocks(int w, int cols, int capacity) {
+    int nblk = (w + cols - 1) / cols;
+    if (nblk > 1 && w - (nblk - 1) * cols + cols <= capacity) --nblk;  // the last block absorbs the remainder
+    return nblk;
+}
+
 template <int D, int PATHS, class CFG, class AR>
 int sweep_capacity(int device) {
     static int cached[16] = {};  // per device; the answer only depends on the kernel and the device
@@ -910,9 +924,13 @@ int sweep_capacity(int device) {
 
 // D = 32-bit words per pixel: the number of disparities for F32Arith, half of it for S16x2Arith (a.d stays the number
 // of disparities).
+// `cols`: columns per block (default: the kernel's capacity CFG::NW).  With fewer, a remainder that still fits the capacity is
+// folded into the last block: 1242 columns = 72 blocks of 17 + one of 18 per view instead of 73 + a block of ONE column, i.e.
+// 146 blocks on the 148 SMs of a B200, so a long single-block kernel of another frame in flight (the median) finds an SM
+// without holding up the whole cooperative grid.
 template <int D, int PATHS, class CFG, class AR = F32Arith<D>>
-bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
-    const int nblk = (a.w + CFG::NW - 1) / CFG::NW;
+bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc, int cols = CFG::NW) {
+    const int nblk = sweep_blocks(a.w, cols, CFG::NW);
     int views_per_launch = a.views;
     if (PATHS == 8) {
         int device = 0;
@@ -950,6 +968,7 @@ bool fused_impl(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) {
         sa.debug = dbg;
     }
 #endif
+    sa.cols = cols;
     sa.h = a.h;
     sa.w = a.w;
     sa.P1 = a.P1;
@@ -1001,35 +1020,35 @@ struct DefaultCfg<128> {
 //     (launches: 1, or 2 when both views do not fit a resident grid) x (columns on the most crowded SM).
 // The default shapes (8 or 10 columns, 2 - 3 blocks per SM) are right for narrow images; when they would stack blocks on
 // some SMs, ONE wide block per SM is better:
-//   Wide17: 17 columns on 19 hardware warps; the two block-edge warps have a warp scheduler to themselves
-//           (sweep_column_of_warp).  KITTI width: 2 x 74 blocks = one per SM of a B200.  1242x375 D=128: 1.22 -> 1.12 ms.
-//   Wide19: 19 columns, for widths whose 17-column grid does not fit the device (the edge warps share their scheduler with
-//           two interior warps; 1242x375 D=128: 1.20 ms).
+//   17 columns per block in the 19-column kernel (19 hardware warps): the two block-edge warps have a warp scheduler to
+//           themselves (sweep_column_of_warp), and a remainder of one or two columns is folded into the last block of the
+//           row.  KITTI width: 2 x 73 blocks on the 148 SMs of a B200.  1242x375 D=128: 1.22 -> 1.12 ms.
+//   Wide19: 19 columns per block, for widths whose 17-column grid does not fit the device (the edge warps share their
+//           scheduler with two interior warps; 1242x375 D=128: 1.20 ms).
 //   Wide13: 13 columns on 15 hardware warps: 1920 columns = 148 blocks, one view per launch.  The only wide shape for 8
 //           values per lane (D = 256): up to 16 warps a block may use 128 registers, with 17 - 20 only 96 (five warps on one
 //           scheduler's 16 K registers), which that body does not fit.
 // All of them keep two rows in flight per warp (four cost more spill traffic in the up sweep than they hide latency); 21
 // hardware warps would cap the kernels at 80 registers (1242x375 D=128: 1.25 ms).
 using Wide13 = SweepCfg<13, 2, 1, 15>;
-using Wide17 = SweepCfg<17, 2, 1, 19>;
 using Wide19 = SweepCfg<19, 2, 1, 19>;
 template <class Def, bool UP_TO_4_PER_LANE>
 int wide_shape(int views, int w) {
     int device = 0, sms = 0;
     cudaGetDevice(&device);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
-    auto cost = [&](int nw, int per_sm) {  // 0: the grid cannot be resident
-        const int nblk = (w + nw - 1) / nw, cap = sms * per_sm;
+    auto cost = [&](int nw, int per_sm, int capacity) {  // 0: the grid cannot be resident
+        const int nblk = sweep_blocks(w, nw, capacity), cap = sms * per_sm;
         if (nblk > cap) return 0;
         const int launches = views * nblk > cap ? views : 1;
         const int per_launch = launches == 1 ? views * nblk : nblk;
         return launches * nw * ((per_launch + sms - 1) / sms);
     };
-    int best = 0, best_cost = cost(Def::NW, Def::MINB);
+    int best = 0, best_cost = cost(Def::NW, Def::MINB, Def::NW);
     const int candidates[3] = {17, 19, 13};
     for (int nw : candidates) {
         if (!UP_TO_4_PER_LANE && nw != 13) continue;
-        const int c = cost(nw, 1);
+        const int c = cost(nw, 1, nw == 13 ? Wide13::NW : Wide19::NW);
         if (c && (!best_cost || c < best_cost)) {
             best = nw;
             best_cost = c;
@@ -1066,6 +1085,11 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
             case 12: return fused_impl<D, 8, SweepCfg<19, 4, 1>>(a, st, lc);
             case 13: return fused_impl<D, 8, typename DefaultCfg<D>::type>(a, st, lc);
             case 16: return fused_impl<D, 8, SweepCfg<19, 2, 1>>(a, st, lc);
+            case 24: return fused_impl<D, 8, SweepCfg<17, 2, 1, 19>>(a, st, lc);        // 17-column kernel: the remainder gets a block of its own
+            case 50: {  // the 19-column kernel with SGM_B200_SWEEP_COLS columns per block
+                static const int cols = [] { const char* e = std::getenv("SGM_B200_SWEEP_COLS"); return e ? std::atoi(e) : 17; }();
+                return fused_impl<D, 8, Wide19>(a, st, lc, cols < 13 ? 13 : (cols > 19 ? 19 : cols));
+            }
             case 21: return fused_impl<D, 8, SweepCfg<17, 4, 1, 19>>(a, st, lc);        // schedulers host 5 5 5 | 2 edge warps
             case 26: return fused_impl<D, 8, SweepCfg<17, 2, 1, 18>>(a, st, lc);        // 5 5 4 | 2 + 1
             case 27: return fused_impl<D, 8, SweepCfg<17, 2, 1, 17>>(a, st, lc);        // 5 4 4 | 2 + 2
@@ -1080,7 +1104,7 @@ bool fused_dispatch(const AggregateArgs& a, cudaStream_t st, LaunchCounter& lc) 
         switch (wide_shape<typename DefaultCfg<D>::type, NARROW>(a.views, a.w)) {
             case 13: return fused_impl<D, 8, Wide13>(a, st, lc);
             case 17:
-                if constexpr (NARROW) return fused_impl<D, 8, Wide17>(a, st, lc);
+                if constexpr (NARROW) return fused_impl<D, 8, Wide19>(a, st, lc, 17);
                 break;
             case 19:
                 if constexpr (NARROW) return fused_impl<D, 8, Wide19>(a, st, lc);
@@ -1121,7 +1145,7 @@ bool fused_dispatch_packed(const AggregateArgs& a0, cudaStream_t st, LaunchCount
         switch (wide_shape<Def, NARROW>(a.views, a.w)) {
             case 13: return fused_impl<DW, 8, Wide13, AR>(a, st, lc);
             case 17:
-                if constexpr (NARROW) return fused_impl<DW, 8, Wide17, AR>(a, st, lc);
+                if constexpr (NARROW) return fused_impl<DW, 8, Wide19, AR>(a, st, lc, 17);
                 break;
             case 19:
                 if constexpr (NARROW) return fused_impl<DW, 8, Wide19, AR>(a, st, lc);
