@@ -335,9 +335,9 @@ constexpr int SWEEP_DOWN = 0, SWEEP_UP = 1, SWEEP_UP_KEEP = 2;
 // steps one after the other) and every row ends at a block barrier, so they set the pace.  A warp's scheduler is
 // (hardware warp id) % 4.  Rule: the edge columns go to hardware warps 3 and 7 (scheduler 3) and, with HELP, their helper
 // warps to 11 and 15; the interior columns fill the warps of schedulers 0 - 2 in hardware order and use scheduler 3's
-// remaining warps only when those are used up; whatever is left of the HWW hardware warps exits.  With NW = HWW = 19 the
-// schedulers host 5 + 5 + 5 interior warps and 2 edge + 2 interior; with NW = 17, HWW = 19 scheduler 3 belongs to the edge
-// warps (and their helpers).  `identity`: tuning-build A/B switch (1242x375 D=128, NW = HWW = 19: 1.249 ms in natural
+// remaining warps only when those are used up; whatever is left of the HWW hardware warps exits.  With 19 columns on 19
+// hardware warps the schedulers host 5 + 5 + 5 interior warps and 2 edge + 2 interior; with 17 columns on 19 hardware warps
+// scheduler 3 belongs to the edge warps (and their helpers).  `identity`: tuning-build A/B switch (1242x375 D=128, NW = HWW = 19: 1.249 ms in natural
 // order, 1.196 ms with this rule).  Blocks of fewer than 9 columns (the ragged last block of a row) use the natural order.
 template <int NW, int HWW, bool HELP>
 __device__ __forceinline__ int sweep_column_of_warp(int hw, int nact, bool identity) {
