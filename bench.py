@@ -543,7 +543,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--inflight", type=int, default=5, help="frames in flight per GPU (engine handles)")
+    ap.add_argument("--inflight", type=int, default=6, help="frames in flight per GPU (engine handles); measured 3..8: profiles/r02_summary.md")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU baseline, the blocking-shell leg and the gpu_sgm baseline")
     ap.add_argument("--no-configs", action="store_true", help="skip the secondary `configs` lines")
     ap.add_argument("--mode", default="reference", choices=sorted(MODES), help="secondary lines: nofilter / integer (see MODES)")
